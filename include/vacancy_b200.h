@@ -1,0 +1,177 @@
+/*
+ * vacancy_b200 - C ABI of the B200-native voxel-carving hot path.
+ *
+ * This is the drop-in boundary for the one path this library accelerates: per-view 2D silhouette
+ * signed-distance field -> multi-view fusion into the voxel grid -> ExtractVoxel / marching cubes.
+ * The reference (unclearness/vacancy) has no FFI of its own: its boundary is the C++ class
+ * vacancy::VoxelCarver (include/vacancy/voxel_carver.h:95-128).  Every entry point below names the
+ * reference interface it replaces; vacancy_b200/shim/voxel_carver_shim.cc implements that C++ class
+ * on top of these calls.
+ *
+ * Conventions
+ *  - plain C, no CUDA or torch types in the signatures; device pointers are passed as void* / typed
+ *    pointers and are documented as such; streams are passed as void* (a cudaStream_t).
+ *  - every call returns VCB_OK (0) or a negative vcb_status; vcb_last_error() gives the text.
+ *    There is no CPU fallback: without a usable CUDA device vcb_create() fails with VCB_ERR_CUDA.
+ *  - images are row-major, x fastest: pixel (x, y) at [y * width + x] (image.h:57-74).
+ *  - the grid is row-major with x fastest: voxel (x, y, z) at [z*nx*ny + y*nx + x]
+ *    (voxel_carver.cc:347-351); state is SoA: float sdf[] and int32 update_num[].
+ *  - all work is ordered on one CUDA stream per carver (vcb_set_stream); calls that take or
+ *    return HOST buffers are complete on return, calls on DEVICE buffers are stream-ordered.
+ *  - a carver is not thread-safe (same as the reference); distinct carvers are independent.
+ */
+#ifndef VACANCY_B200_H_
+#define VACANCY_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum vcb_status {
+  VCB_OK = 0,
+  VCB_ERR_INVALID = -1,   /* bad argument / option the reference's Init() would reject */
+  VCB_ERR_CUDA = -2,      /* CUDA runtime error (text in vcb_last_error) */
+  VCB_ERR_STATE = -3,     /* call out of order (e.g. fill before count) */
+  VCB_ERR_UNSUPPORTED = -4
+} vcb_status;
+
+/* VoxelUpdate / SdfInterpolation / UpdateOutsideImage, voxel_carver.h:20-37 (same values) */
+enum { VCB_UPDATE_MAX = 0, VCB_UPDATE_WEIGHTED_AVERAGE = 1 };
+enum { VCB_INTERP_NN = 0, VCB_INTERP_BILINEAR = 1 };
+enum { VCB_OUTSIDE_NONE = 0, VCB_OUTSIDE_MAX = 1 };
+/* concrete camera models, camera.h:66 (PinholeCamera) and camera.h:116 (OrthoCamera) */
+enum { VCB_CAMERA_PINHOLE = 0, VCB_CAMERA_ORTHO = 1 };
+
+/* VoxelCarverOption + VoxelUpdateOption, voxel_carver.h:43-60, field for field, followed by the
+ * placement fields this library adds.  Zero-initialise, then call vcb_options_default(). */
+typedef struct vcb_options {
+  float bb_max[3];
+  float bb_min[3];
+  float resolution;             /* default 0.1f */
+  int32_t sdf_minmax_normalize; /* default 1 */
+  int32_t voxel_update;         /* default VCB_UPDATE_MAX */
+  int32_t sdf_interp;           /* default VCB_INTERP_BILINEAR */
+  int32_t update_outside;       /* default VCB_OUTSIDE_NONE */
+  int32_t voxel_max_update_num; /* default 255 */
+  float voxel_update_weight;    /* default 1.0f */
+  int32_t use_truncation;       /* default 0 */
+  float truncation_band;        /* default 0.1f */
+  /* --- additions --- */
+  int32_t device;  /* CUDA device ordinal (default 0) */
+  int32_t z_begin; /* this carver owns the z planes [z_begin, z_end) of the global grid; */
+  int32_t z_end;   /* z_begin == z_end == 0 selects the whole grid (single GPU) */
+} vcb_options;
+
+/* One view: camera.w2c().cast<float>() (voxel_carver.cc:438) as a row-major 3x4, the projection
+ * model with its intrinsics (camera.cc:131-137 / 201-205), the image size and the inclusive ROI
+ * (voxel_carver.cc:394-413). */
+typedef struct vcb_view {
+  float w2c[12];
+  int32_t model;
+  float fx, fy, cx, cy;
+  int32_t width, height;
+  int32_t roi_min[2];
+  int32_t roi_max[2];
+} vcb_view;
+
+typedef struct vcb_carver vcb_carver;
+
+/* Text of the last error on this carver; with NULL, of the last failed vcb_create / free call
+ * of the calling thread. Never NULL. */
+const char* vcb_last_error(const vcb_carver* c);
+
+/* InvalidSdf::kVal, voxel_carver.cc:100 */
+float vcb_invalid_sdf(void);
+
+/* Fills the reference's defaults (voxel_carver.h:43-60). */
+void vcb_options_default(vcb_options* opt);
+
+/* VoxelCarver::set_option + Init, voxel_carver.cc:371-392 and VoxelGrid::Init :276-345.
+ * Rejects what Init() rejects (max_update_num < 1, weight / band / resolution not positive,
+ * empty bounding box) with VCB_ERR_INVALID.  Unlike the reference, grids above 2^31 voxels are
+ * accepted (64-bit indices); a single carver's slab must still hold < 2^31 * 32 voxels. */
+int vcb_create(const vcb_options* opt, vcb_carver** out);
+/* VoxelCarver::~VoxelCarver, voxel_carver.cc:369 */
+void vcb_destroy(vcb_carver* c);
+
+/* VoxelGrid::voxel_num, voxel_carver.cc:347: global grid size; slab = owned z range */
+int vcb_grid_dims(const vcb_carver* c, int32_t dims3[3]);
+int vcb_slab_range(const vcb_carver* c, int32_t* z_begin, int32_t* z_end);
+/* Voxel::pos along each axis (voxel_carver.cc:315-326), global tables of nx, ny, nz floats (host) */
+int vcb_grid_positions(const vcb_carver* c, float* px, float* py, float* pz);
+
+/* All later work of this carver is issued on `cuda_stream` (a cudaStream_t; NULL = the legacy
+ * default stream). Synchronises the previous stream first. */
+int vcb_set_stream(vcb_carver* c, void* cuda_stream);
+/* Launches any queued fusion work and waits for the carver's stream. */
+int vcb_synchronize(vcb_carver* c);
+/* Launches the fusion of every view queued so far (views are queued by the carve calls and fused
+ * in call order, up to 64 per kernel launch); does not wait. Extract / download calls flush
+ * implicitly, so this is only needed for timing. */
+int vcb_flush(vcb_carver* c);
+
+/* Carve(camera, silhouette, roi_min, roi_max, sdf*) for n views, voxel_carver.cc:394-413:
+ * builds each view's 2D SDF from its mask (MakeSignedDistanceField :169-237 with the carver's
+ * normalize / truncation options) and fuses it (:415-496).  masks[i]: HOST uint8 image of
+ * views[i].width x height.  sdf_out: NULL, or n HOST float pointers (entries may be NULL) that
+ * receive each view's 2D SDF like the reference's `Image1f* sdf` out-parameter. */
+int vcb_carve_masks(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                    const uint8_t* const* masks, float* const* sdf_out);
+/* Same with masks already in DEVICE memory (stream-ordered; masks must stay valid until the
+ * carver's stream has passed this call). sdf_out_dev: NULL or n DEVICE float pointers. */
+int vcb_carve_masks_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                           const uint8_t* const* masks_dev, float* const* sdf_out_dev);
+/* Carve(camera, roi_min, roi_max, sdf) for n views, voxel_carver.cc:415-496; HOST float SDFs */
+int vcb_carve_sdfs(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                   const float* const* sdfs);
+/* Same with DEVICE float SDF images, fused in place (no copy): flushes earlier queued views,
+ * then launches these; the images must stay valid until the stream has passed this call. */
+int vcb_carve_sdfs_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                          const float* const* sdfs_dev);
+
+/* Free functions of voxel_carver.h:120-126 on HOST buffers, run on CUDA device `device`.
+ * DistanceTransformL1 (voxel_carver.cc:102-167) and MakeSignedDistanceField (:169-237). */
+int vcb_distance_transform_l1(int32_t device, const uint8_t* mask, int32_t width, int32_t height,
+                              const int32_t roi_min[2], const int32_t roi_max[2], float* dist);
+int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t width,
+                                   int32_t height, const int32_t roi_min[2],
+                                   const int32_t roi_max[2], int32_t minmax_normalize,
+                                   int32_t use_truncation, float truncation_band, float* dist);
+
+/* ExtractIsoSurface(mesh, iso_level, linear_interp), voxel_carver.cc:540-543 ->
+ * MarchingCubes marching_cubes.cc:63-228, two-phase: _count runs the extraction on the device and
+ * reports the sizes, _fill copies the mesh into HOST buffers (3 floats per vertex, 3 int32 per
+ * face, same vertex numbering and face order as the reference). */
+int vcb_extract_iso_count(vcb_carver* c, double iso_level, int32_t linear_interp,
+                          int64_t* n_vertices, int64_t* n_faces);
+int vcb_extract_iso_fill(vcb_carver* c, float* vertices, int32_t* faces);
+/* DEVICE pointers to the mesh left by the last vcb_extract_iso_count (owned by the carver, valid
+ * until its next extract call or destroy). */
+int vcb_extract_iso_device(vcb_carver* c, const float** vertices_dev, const int32_t** faces_dev);
+
+/* ExtractVoxel(mesh, inside_empty), voxel_carver.cc:530-538 -> extract_voxel.cc:258-317.
+ * _count classifies the voxels and returns how many cubes will be emitted (24 vertices and 12
+ * faces each); _fill writes them to HOST buffers in the reference's raster order;
+ * _occupancy writes one byte per owned voxel (1 = emitted) to a HOST buffer instead. */
+int vcb_extract_voxel_count(vcb_carver* c, int32_t inside_empty, int64_t* n_voxels);
+int vcb_extract_voxel_fill(vcb_carver* c, float* vertices, int32_t* faces);
+int vcb_extract_voxel_occupancy(vcb_carver* c, uint8_t* flags);
+
+/* Grid state of the owned slab to / from HOST buffers (the reference keeps the grid private,
+ * voxel_carver.h:97; tests and checkpoints use these). Either pointer may be NULL. */
+int vcb_download_grid(vcb_carver* c, float* sdf, int32_t* update_num);
+int vcb_upload_grid(vcb_carver* c, const float* sdf, const int32_t* update_num);
+/* DEVICE pointers to the owned slab's state (stream-ordered access only). */
+int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev);
+
+/* Device time in milliseconds spent by this carver's kernels since the last call, by stage:
+ * [0] 2D SDF, [1] fusion, [2] ExtractVoxel, [3] marching cubes; launches[4] likewise counts kernel
+ * launches. Measured with CUDA events on the carver's stream; calling it synchronises. */
+int vcb_stage_times(vcb_carver* c, float ms[4], int64_t launches[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VACANCY_B200_H_ */

@@ -1,0 +1,100 @@
+"""ctypes binding of the C ABI in include/vacancy_b200.h (one-to-one, no logic)."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libvacancy_b200.so")
+
+
+class LibraryMissing(RuntimeError):
+    pass
+
+
+class VcbError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("vacancy_b200 error %d: %s" % (code, text))
+        self.code = code
+
+
+class Options(C.Structure):
+    """vcb_options (include/vacancy_b200.h) = VoxelCarverOption + VoxelUpdateOption + placement."""
+    _fields_ = [("bb_max", C.c_float * 3), ("bb_min", C.c_float * 3), ("resolution", C.c_float),
+                ("sdf_minmax_normalize", C.c_int32), ("voxel_update", C.c_int32),
+                ("sdf_interp", C.c_int32), ("update_outside", C.c_int32),
+                ("voxel_max_update_num", C.c_int32), ("voxel_update_weight", C.c_float),
+                ("use_truncation", C.c_int32), ("truncation_band", C.c_float),
+                ("device", C.c_int32), ("z_begin", C.c_int32), ("z_end", C.c_int32)]
+
+
+class View(C.Structure):
+    """vcb_view."""
+    _fields_ = [("w2c", C.c_float * 12), ("model", C.c_int32), ("fx", C.c_float),
+                ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("width", C.c_int32),
+                ("height", C.c_int32), ("roi_min", C.c_int32 * 2), ("roi_max", C.c_int32 * 2)]
+
+
+EXPORTS = [
+    "vcb_last_error", "vcb_invalid_sdf", "vcb_options_default", "vcb_create", "vcb_destroy",
+    "vcb_grid_dims", "vcb_slab_range", "vcb_grid_positions", "vcb_set_stream", "vcb_synchronize",
+    "vcb_flush", "vcb_carve_masks", "vcb_carve_masks_device", "vcb_carve_sdfs",
+    "vcb_carve_sdfs_device", "vcb_distance_transform_l1", "vcb_make_signed_distance_field",
+    "vcb_extract_iso_count", "vcb_extract_iso_fill", "vcb_extract_iso_device",
+    "vcb_extract_voxel_count", "vcb_extract_voxel_fill", "vcb_extract_voxel_occupancy",
+    "vcb_download_grid", "vcb_upload_grid", "vcb_grid_device", "vcb_stage_times",
+]
+
+_lib = None
+
+
+def load_library(path=LIB_PATH):
+    """Loads libvacancy_b200.so; raises LibraryMissing (never falls back) when it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise LibraryMissing(
+            "%s not found: build it with `python -m vacancy_b200.build` "
+            "(there is no CPU fallback)" % path)
+    L = C.CDLL(path)
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    fp, ip, u8p = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_uint8)
+    L.vcb_last_error.restype = C.c_char_p
+    L.vcb_last_error.argtypes = [vp]
+    L.vcb_invalid_sdf.restype = C.c_float
+    L.vcb_options_default.argtypes = [C.POINTER(Options)]
+    L.vcb_options_default.restype = None
+    L.vcb_create.argtypes = [C.POINTER(Options), C.POINTER(vp)]
+    L.vcb_destroy.argtypes = [vp]
+    L.vcb_destroy.restype = None
+    L.vcb_grid_dims.argtypes = [vp, ip]
+    L.vcb_slab_range.argtypes = [vp, ip, ip]
+    L.vcb_grid_positions.argtypes = [vp, fp, fp, fp]
+    L.vcb_set_stream.argtypes = [vp, vp]
+    L.vcb_synchronize.argtypes = [vp]
+    L.vcb_flush.argtypes = [vp]
+    pp = C.POINTER(vp)
+    L.vcb_carve_masks.argtypes = [vp, i32, C.POINTER(View), pp, pp]
+    L.vcb_carve_masks_device.argtypes = [vp, i32, C.POINTER(View), pp, pp]
+    L.vcb_carve_sdfs.argtypes = [vp, i32, C.POINTER(View), pp]
+    L.vcb_carve_sdfs_device.argtypes = [vp, i32, C.POINTER(View), pp]
+    L.vcb_distance_transform_l1.argtypes = [i32, u8p, i32, i32, ip, ip, fp]
+    L.vcb_make_signed_distance_field.argtypes = [i32, u8p, i32, i32, ip, ip, i32, i32, C.c_float,
+                                                 fp]
+    L.vcb_extract_iso_count.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
+    L.vcb_extract_iso_fill.argtypes = [vp, fp, ip]
+    L.vcb_extract_iso_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    L.vcb_extract_voxel_count.argtypes = [vp, i32, C.POINTER(i64)]
+    L.vcb_extract_voxel_fill.argtypes = [vp, fp, ip]
+    L.vcb_extract_voxel_occupancy.argtypes = [vp, u8p]
+    L.vcb_download_grid.argtypes = [vp, fp, ip]
+    L.vcb_upload_grid.argtypes = [vp, fp, ip]
+    L.vcb_grid_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    L.vcb_stage_times.argtypes = [vp, fp, C.POINTER(i64)]
+    _lib = L
+    return L
+
+
+def check(L, handle, rc):
+    if rc != 0:
+        text = L.vcb_last_error(handle)
+        raise VcbError(rc, text.decode() if text else "")

@@ -1,0 +1,792 @@
+// The carver handle and the C ABI (include/vacancy_b200.h): device state, view queue, stream
+// plumbing.  Mirrors vacancy::VoxelCarver (voxel_carver.h:95-118, voxel_carver.cc:367-543) for the
+// carving hot path; the kernels are in sdf2d.cu, fusion.cu, extract_voxel.cu, marching_cubes.cu.
+//
+// Device layout (all SoA, x fastest):
+//   sdf[]        float  per owned voxel (+ up to 2 halo planes below the slab for marching cubes)
+//   update_num[] int32  per owned voxel
+//   pos_x/y/z[]  float  voxel-centre tables of the GLOBAL grid (voxel_carver.cc:315-326)
+//   image pool   kMaxViewsPerLaunch float SDF images waiting to be fused
+//   SDF scratch  kSdfSubBatch x (mask copy + 2 int16 images)
+#include <float.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+using namespace vcb;
+
+namespace {
+
+thread_local std::string g_last_error = "";
+
+struct TimedSpan {
+  cudaEvent_t a, b;
+  int stage;
+};
+
+}  // namespace
+
+struct vcb_carver {
+  vcb_options opt;
+  int nx = 0, ny = 0, nz = 0;
+  int z_begin = 0, z_end = 0;
+  int halo = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+
+  float* sdf_alloc = nullptr;  // halo planes first
+  float* sdf = nullptr;        // plane z_begin
+  int32_t* un = nullptr;
+  float *pos_x = nullptr, *pos_y = nullptr, *pos_z = nullptr;
+  std::vector<float> h_pos[3];
+  float2* wtab = nullptr;
+  int wtab_n = 0;
+  bool un_implied = true;  // update_num < 1  <=>  sdf == kVal (true unless a grid was uploaded)
+
+  // queued views
+  FuseParams fp;
+  int pending = 0;
+  Scratch pool;          // kMaxViewsPerLaunch image slots
+  size_t slot_floats = 0;
+  Scratch max_sdf;       // one float per slot
+  // 2D SDF scratch
+  Scratch mask_stage, rowd, cold, absmax, sdf_views;
+  size_t sdf_pix = 0;
+
+  VoxelExtract vox;
+  IsoExtract iso;
+
+  bool timing = true;
+  std::vector<TimedSpan> spans;
+  float stage_ms[4] = {0, 0, 0, 0};
+  int64_t stage_launches[4] = {0, 0, 0, 0};
+};
+
+namespace {
+
+int fail(vcb_carver* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (c) {
+    c->err = buf;
+  }
+  g_last_error = buf;
+  return code;
+}
+
+#define CU(c, call)                                                                          \
+  do {                                                                                       \
+    cudaError_t e_ = (call);                                                                 \
+    if (e_ != cudaSuccess)                                                                   \
+      return fail(c, VCB_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                  __LINE__);                                                                 \
+  } while (0)
+
+std::mutex g_init_mutex;
+bool g_tables_ready[64] = {false};
+
+int use_device(vcb_carver* c, int device) {
+  CU(c, cudaSetDevice(device));
+  std::lock_guard<std::mutex> lock(g_init_mutex);
+  if (device >= 0 && device < 64 && !g_tables_ready[device]) {
+    init_mc_tables();
+    CU(c, cudaGetLastError());
+    g_tables_ready[device] = true;
+  }
+  return VCB_OK;
+}
+
+struct Span {
+  vcb_carver* c;
+  int stage;
+  cudaEvent_t a = nullptr, b = nullptr;
+  Span(vcb_carver* c_, int stage_) : c(c_), stage(stage_) {
+    if (c->timing) {
+      cudaEventCreate(&a);
+      cudaEventCreate(&b);
+      cudaEventRecord(a, c->stream);
+    }
+  }
+  ~Span() {
+    if (c->timing) {
+      cudaEventRecord(b, c->stream);
+      c->spans.push_back({a, b, stage});
+    }
+  }
+};
+
+void resolve_spans(vcb_carver* c) {
+  for (auto& s : c->spans) {
+    float ms = 0;
+    cudaEventSynchronize(s.b);
+    if (cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) c->stage_ms[s.stage] += ms;
+    cudaEventDestroy(s.a);
+    cudaEventDestroy(s.b);
+  }
+  c->spans.clear();
+}
+
+// voxel_carver.cc:375-389 and :276-301
+int validate(const vcb_options* o, int dims[3]) {
+  if (o->voxel_max_update_num < 1) return fail(nullptr, VCB_ERR_INVALID, "voxel_max_update_num must be positive");
+  if (!(o->voxel_update_weight >= FLT_MIN)) return fail(nullptr, VCB_ERR_INVALID, "voxel_update_weight must be positive");
+  if (!(o->truncation_band >= FLT_MIN)) return fail(nullptr, VCB_ERR_INVALID, "truncation_band must be positive");
+  if (!(o->resolution >= FLT_MIN)) return fail(nullptr, VCB_ERR_INVALID, "resolution must be positive %f", o->resolution);
+  if (o->bb_max[0] <= o->bb_min[0] || o->bb_max[1] <= o->bb_min[1] || o->bb_max[2] <= o->bb_min[2])
+    return fail(nullptr, VCB_ERR_INVALID, "input bounding box is invalid");
+  if (o->voxel_update != VCB_UPDATE_MAX && o->voxel_update != VCB_UPDATE_WEIGHTED_AVERAGE)
+    return fail(nullptr, VCB_ERR_INVALID, "unknown voxel_update %d", o->voxel_update);
+  if (o->sdf_interp != VCB_INTERP_NN && o->sdf_interp != VCB_INTERP_BILINEAR)
+    return fail(nullptr, VCB_ERR_INVALID, "unknown sdf_interp %d", o->sdf_interp);
+  if (o->update_outside != VCB_OUTSIDE_NONE && o->update_outside != VCB_OUTSIDE_MAX)
+    return fail(nullptr, VCB_ERR_INVALID, "unknown update_outside %d", o->update_outside);
+  for (int i = 0; i < 3; i++) {
+    const float diff = o->bb_max[i] - o->bb_min[i];
+    const float q = diff / o->resolution;  // voxel_carver.cc:294-296 (truncating cast)
+    if (!(q < 2147483648.0f)) return fail(nullptr, VCB_ERR_INVALID, "too many voxels");
+    dims[i] = (int)q;
+    if (dims[i] < 1) return fail(nullptr, VCB_ERR_INVALID, "bounding box smaller than one voxel");
+  }
+  return VCB_OK;
+}
+
+int check_view(vcb_carver* c, const vcb_view& v) {
+  if (v.width < 1 || v.height < 1 || v.width > kMaxImageDim || v.height > kMaxImageDim)
+    return fail(c, VCB_ERR_INVALID, "image size %dx%d out of range (max %d)", v.width, v.height,
+                kMaxImageDim);
+  if (v.roi_min[0] < 0 || v.roi_min[1] < 0 || v.roi_max[0] >= v.width || v.roi_max[1] >= v.height ||
+      v.roi_min[0] > v.roi_max[0] || v.roi_min[1] > v.roi_max[1])
+    return fail(c, VCB_ERR_INVALID, "roi [%d,%d]-[%d,%d] outside the %dx%d image", v.roi_min[0],
+                v.roi_min[1], v.roi_max[0], v.roi_max[1], v.width, v.height);
+  if (v.model != VCB_CAMERA_PINHOLE && v.model != VCB_CAMERA_ORTHO)
+    return fail(c, VCB_ERR_UNSUPPORTED, "camera model %d: only pinhole and ortho are supported", v.model);
+  return VCB_OK;
+}
+
+void fill_fuse_view(FuseView* f, const vcb_view& v, const float* image, const float* max_sdf) {
+  memcpy(f->m, v.w2c, sizeof(f->m));
+  f->fx = v.fx;
+  f->fy = v.fy;
+  f->cx = v.cx;
+  f->cy = v.cy;
+  f->roi_min_x = (float)v.roi_min[0];
+  f->roi_min_y = (float)v.roi_min[1];
+  f->roi_max_x = (float)v.roi_max[0];
+  f->roi_max_y = (float)v.roi_max[1];
+  f->roi_min_xi = v.roi_min[0];
+  f->roi_min_yi = v.roi_min[1];
+  f->roi_max_xi = v.roi_max[0];
+  f->roi_max_yi = v.roi_max[1];
+  f->pitch = v.width;
+  f->model = v.model;
+  f->image = image;
+  f->max_sdf = max_sdf;
+}
+
+GridDesc grid_desc(const vcb_carver* c) {
+  GridDesc g;
+  g.sdf = c->sdf;
+  g.update_num = c->un;
+  g.pos_x = c->pos_x;
+  g.pos_y = c->pos_y;
+  g.pos_z = c->pos_z;
+  g.nx = c->nx;
+  g.ny = c->ny;
+  g.nz = c->nz;
+  g.z_begin = c->z_begin;
+  g.z_end = c->z_end;
+  g.halo = c->halo;
+  g.resolution = c->opt.resolution;
+  return g;
+}
+
+int64_t slab_voxels(const vcb_carver* c) {
+  return (int64_t)c->nx * c->ny * (c->z_end - c->z_begin);
+}
+
+// launches the fusion kernel over the queued views
+int flush_pending(vcb_carver* c) {
+  if (c->pending == 0) return VCB_OK;
+  c->fp.n_views = c->pending;
+  {
+    Span span(c, 1);
+    launch_fusion(c->fp, c->opt.sdf_interp, c->opt.voxel_update, c->stream, &c->stage_launches[1]);
+  }
+  c->pending = 0;
+  CU(c, cudaGetLastError());
+  return VCB_OK;
+}
+
+int ensure_pool(vcb_carver* c, size_t floats_per_image) {
+  if (floats_per_image <= c->slot_floats && c->pool.ptr) return VCB_OK;
+  int rc = flush_pending(c);
+  if (rc != VCB_OK) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  CU(c, c->pool.reserve(floats_per_image * sizeof(float) * kMaxViewsPerLaunch));
+  c->slot_floats = floats_per_image;
+  return VCB_OK;
+}
+
+int ensure_sdf_scratch(vcb_carver* c, size_t pix) {
+  if (pix <= c->sdf_pix && c->rowd.ptr) return VCB_OK;
+  CU(c, cudaStreamSynchronize(c->stream));
+  CU(c, c->mask_stage.reserve(pix * kSdfSubBatch));
+  CU(c, c->rowd.reserve(pix * kSdfSubBatch * sizeof(int16_t)));
+  CU(c, c->cold.reserve(pix * kSdfSubBatch * sizeof(int16_t)));
+  CU(c, c->absmax.reserve(sizeof(int) * kSdfSubBatch));
+  CU(c, c->sdf_views.reserve(sizeof(SdfView) * kSdfSubBatch));
+  c->sdf_pix = pix;
+  return VCB_OK;
+}
+
+// shared body of vcb_carve_masks / vcb_carve_masks_device
+int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                     const uint8_t* const* masks, float* const* sdf_out, bool device_io) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (n_views < 0 || (n_views > 0 && (!views || !masks))) return fail(c, VCB_ERR_INVALID, "null argument");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  size_t max_pix = 0;
+  for (int i = 0; i < n_views; i++) {
+    if ((rc = check_view(c, views[i])) != VCB_OK) return rc;
+    if (!masks[i]) return fail(c, VCB_ERR_INVALID, "mask %d is null", i);
+    max_pix = max(max_pix, (size_t)views[i].width * views[i].height);
+  }
+  if (n_views == 0) return VCB_OK;
+  if ((rc = ensure_pool(c, max_pix)) != VCB_OK) return rc;
+  if ((rc = ensure_sdf_scratch(c, max_pix)) != VCB_OK) return rc;
+  float* pool = static_cast<float*>(c->pool.ptr);
+  float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
+  for (int first = 0; first < n_views;) {
+    int nb = min(kSdfSubBatch, n_views - first);
+    nb = min(nb, kMaxViewsPerLaunch - c->pending);
+    SdfView hv[kSdfSubBatch];
+    for (int i = 0; i < nb; i++) {
+      const vcb_view& v = views[first + i];
+      const size_t pix = (size_t)v.width * v.height;
+      const int slot = c->pending + i;
+      if (device_io) {
+        hv[i].mask = masks[first + i];
+      } else {
+        uint8_t* dst = static_cast<uint8_t*>(c->mask_stage.ptr) + (size_t)i * c->sdf_pix;
+        CU(c, cudaMemcpyAsync(dst, masks[first + i], pix, cudaMemcpyHostToDevice, c->stream));
+        hv[i].mask = dst;
+      }
+      hv[i].out = pool + (size_t)slot * c->slot_floats;
+      hv[i].rowd = static_cast<int16_t*>(c->rowd.ptr) + (size_t)i * c->sdf_pix;
+      hv[i].cold = static_cast<int16_t*>(c->cold.ptr) + (size_t)i * c->sdf_pix;
+      hv[i].absmax = static_cast<int*>(c->absmax.ptr) + i;
+      hv[i].max_out = max_sdf + slot;
+      hv[i].width = v.width;
+      hv[i].height = v.height;
+      hv[i].rx0 = v.roi_min[0];
+      hv[i].ry0 = v.roi_min[1];
+      hv[i].rx1 = v.roi_max[0];
+      hv[i].ry1 = v.roi_max[1];
+      fill_fuse_view(&c->fp.views[slot], v, hv[i].out, hv[i].max_out);
+    }
+    // the descriptor array is small: pass it through a pageable async copy (staged by the driver)
+    CU(c, cudaMemcpyAsync(c->sdf_views.ptr, hv, sizeof(SdfView) * nb, cudaMemcpyHostToDevice,
+                          c->stream));
+    {
+      Span span(c, 0);
+      launch_sdf2d(static_cast<SdfView*>(c->sdf_views.ptr), hv, nb, kSdfSigned,
+                   c->opt.sdf_minmax_normalize, c->opt.use_truncation, c->opt.truncation_band,
+                   c->stream, &c->stage_launches[0]);
+    }
+    CU(c, cudaGetLastError());
+    if (sdf_out) {
+      for (int i = 0; i < nb; i++) {
+        if (!sdf_out[first + i]) continue;
+        const size_t bytes = (size_t)hv[i].width * hv[i].height * sizeof(float);
+        CU(c, cudaMemcpyAsync(sdf_out[first + i], hv[i].out, bytes,
+                              device_io ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
+                              c->stream));
+      }
+    }
+    c->pending += nb;
+    first += nb;
+    if (c->pending == kMaxViewsPerLaunch) {
+      if ((rc = flush_pending(c)) != VCB_OK) return rc;
+    }
+  }
+  if (!device_io) {
+    // host buffers are borrowed for the duration of the call only (voxel_carver.cc:394-413)
+    CU(c, cudaStreamSynchronize(c->stream));
+  }
+  return VCB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* vcb_last_error(const vcb_carver* c) { return c ? c->err.c_str() : g_last_error.c_str(); }
+
+float vcb_invalid_sdf(void) { return kInvalidSdf; }
+
+void vcb_options_default(vcb_options* o) {
+  memset(o, 0, sizeof(*o));
+  o->resolution = 0.1f;
+  o->sdf_minmax_normalize = 1;
+  o->voxel_update = VCB_UPDATE_MAX;
+  o->sdf_interp = VCB_INTERP_BILINEAR;
+  o->update_outside = VCB_OUTSIDE_NONE;
+  o->voxel_max_update_num = 255;
+  o->voxel_update_weight = 1.0f;
+  o->use_truncation = 0;
+  o->truncation_band = 0.1f;
+}
+
+int vcb_create(const vcb_options* opt, vcb_carver** out) {
+  if (!opt || !out) return fail(nullptr, VCB_ERR_INVALID, "null argument");
+  *out = nullptr;
+  int dims[3];
+  int rc = validate(opt, dims);
+  if (rc != VCB_OK) return rc;
+  int z0 = opt->z_begin, z1 = opt->z_end;
+  if (z0 == 0 && z1 == 0) z1 = dims[2];
+  if (z0 < 0 || z1 > dims[2] || z0 >= z1)
+    return fail(nullptr, VCB_ERR_INVALID, "z slab [%d,%d) outside the grid of %d planes", z0, z1, dims[2]);
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev < 1)
+    return fail(nullptr, VCB_ERR_CUDA, "no CUDA device: %s (this library has no CPU fallback)",
+                cudaGetErrorString(e));
+  if (opt->device < 0 || opt->device >= n_dev)
+    return fail(nullptr, VCB_ERR_INVALID, "device %d not in [0,%d)", opt->device, n_dev);
+
+  vcb_carver* c = new vcb_carver;
+  c->opt = *opt;
+  c->nx = dims[0];
+  c->ny = dims[1];
+  c->nz = dims[2];
+  c->z_begin = z0;
+  c->z_end = z1;
+  c->halo = z0 < 2 ? z0 : 2;
+#define CREATE_TRY(call)                                                                     \
+  do {                                                                                       \
+    cudaError_t e_ = (call);                                                                 \
+    if (e_ != cudaSuccess) {                                                                 \
+      fail(nullptr, VCB_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_));                   \
+      vcb_destroy(c);                                                                        \
+      return VCB_ERR_CUDA;                                                                   \
+    }                                                                                        \
+  } while (0)
+  if (use_device(c, opt->device) != VCB_OK) {
+    g_last_error = c->err;
+    delete c;
+    return VCB_ERR_CUDA;
+  }
+  const size_t plane = (size_t)c->nx * c->ny;
+  const size_t n = plane * (size_t)(z1 - z0);
+  CREATE_TRY(cudaMalloc(&c->sdf_alloc, (n + plane * c->halo) * sizeof(float)));
+  c->sdf = c->sdf_alloc + plane * c->halo;
+  CREATE_TRY(cudaMalloc(&c->un, n * sizeof(int32_t)));
+  // voxel centres: diff * (float(k) / float(n)) + bb_min + resolution * 0.5f, voxel_carver.cc:309-326
+  const float offset = opt->resolution * 0.5f;
+  float** dpos[3] = {&c->pos_x, &c->pos_y, &c->pos_z};
+  for (int a = 0; a < 3; a++) {
+    const float diff = opt->bb_max[a] - opt->bb_min[a];
+    c->h_pos[a].resize(dims[a]);
+    for (int k = 0; k < dims[a]; k++) {
+      volatile float frac = (float)k / (float)dims[a];
+      volatile float t = diff * frac;
+      volatile float t2 = t + opt->bb_min[a];
+      c->h_pos[a][k] = t2 + offset;
+    }
+    CREATE_TRY(cudaMalloc(dpos[a], dims[a] * sizeof(float)));
+    CREATE_TRY(cudaMemcpy(*dpos[a], c->h_pos[a].data(), dims[a] * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  // weighted-average factors by update count, voxel_carver.cc:91-93
+  c->wtab_n = opt->voxel_max_update_num < 4096 ? opt->voxel_max_update_num + 2 : 4098;
+  {
+    std::vector<float2> t(c->wtab_n);
+    const float w = opt->voxel_update_weight;
+    for (int k = 0; k < c->wtab_n; k++) {
+      volatile float wn = w * (float)k;
+      volatile float den = w * (float)(k + 1);
+      volatile float inv = 1.0f / den;
+      t[k].x = wn;
+      t[k].y = inv;
+    }
+    CREATE_TRY(cudaMalloc(&c->wtab, c->wtab_n * sizeof(float2)));
+    CREATE_TRY(cudaMemcpy(c->wtab, t.data(), c->wtab_n * sizeof(float2), cudaMemcpyHostToDevice));
+  }
+  CREATE_TRY(c->max_sdf.reserve(sizeof(float) * kMaxViewsPerLaunch));
+  // sdf = kVal, update_num = 0 (voxel_carver.cc:342, voxel_carver.h:67-68)
+  {
+    // -FLT_MAX is 0xFF7FFFFF: not a byte pattern, so fill through a tiny kernel-free path:
+    std::vector<float> row(plane, kInvalidSdf);
+    for (int z = 0; z < (z1 - z0) + c->halo; z++) {
+      CREATE_TRY(cudaMemcpy(c->sdf_alloc + (size_t)z * plane, row.data(), plane * sizeof(float),
+                            cudaMemcpyHostToDevice));
+    }
+    CREATE_TRY(cudaMemset(c->un, 0, n * sizeof(int32_t)));
+  }
+  memset(&c->fp, 0, sizeof(c->fp));
+  c->fp.sdf = c->sdf;
+  c->fp.update_num = c->un;
+  c->fp.pos_x = c->pos_x;
+  c->fp.pos_y = c->pos_y;
+  c->fp.pos_z = c->pos_z;
+  c->fp.wtab = c->wtab;
+  c->fp.wtab_n = c->wtab_n;
+  c->fp.nx = c->nx;
+  c->fp.ny = c->ny;
+  c->fp.z_begin = z0;
+  c->fp.z_end = z1;
+  c->fp.max_update_num = opt->voxel_max_update_num;
+  c->fp.use_truncation = opt->use_truncation;
+  c->fp.update_outside = opt->update_outside;
+  c->fp.weight = opt->voxel_update_weight;
+#undef CREATE_TRY
+  *out = c;
+  return VCB_OK;
+}
+
+void vcb_destroy(vcb_carver* c) {
+  if (!c) return;
+  cudaSetDevice(c->opt.device);
+  cudaStreamSynchronize(c->stream);
+  resolve_spans(c);
+  cudaFree(c->sdf_alloc);
+  cudaFree(c->un);
+  cudaFree(c->pos_x);
+  cudaFree(c->pos_y);
+  cudaFree(c->pos_z);
+  cudaFree(c->wtab);
+  Scratch* all[] = {&c->pool, &c->max_sdf, &c->mask_stage, &c->rowd, &c->cold, &c->absmax,
+                    &c->sdf_views, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
+                    &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
+                    &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
+                    &c->iso.verts, &c->iso.faces, &c->iso.counters};
+  for (Scratch* s : all) s->release();
+  delete c;
+}
+
+int vcb_grid_dims(const vcb_carver* c, int32_t dims3[3]) {
+  if (!c || !dims3) return fail(nullptr, VCB_ERR_INVALID, "null argument");
+  dims3[0] = c->nx;
+  dims3[1] = c->ny;
+  dims3[2] = c->nz;
+  return VCB_OK;
+}
+
+int vcb_slab_range(const vcb_carver* c, int32_t* z_begin, int32_t* z_end) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null argument");
+  if (z_begin) *z_begin = c->z_begin;
+  if (z_end) *z_end = c->z_end;
+  return VCB_OK;
+}
+
+int vcb_grid_positions(const vcb_carver* c, float* px, float* py, float* pz) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null argument");
+  if (px) memcpy(px, c->h_pos[0].data(), c->nx * sizeof(float));
+  if (py) memcpy(py, c->h_pos[1].data(), c->ny * sizeof(float));
+  if (pz) memcpy(pz, c->h_pos[2].data(), c->nz * sizeof(float));
+  return VCB_OK;
+}
+
+int vcb_set_stream(vcb_carver* c, void* cuda_stream) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  if ((rc = flush_pending(c)) != VCB_OK) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  c->stream = static_cast<cudaStream_t>(cuda_stream);
+  return VCB_OK;
+}
+
+int vcb_flush(vcb_carver* c) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  return flush_pending(c);
+}
+
+int vcb_synchronize(vcb_carver* c) {
+  int rc = vcb_flush(c);
+  if (rc != VCB_OK) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  return VCB_OK;
+}
+
+int vcb_carve_masks(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                    const uint8_t* const* masks, float* const* sdf_out) {
+  return carve_masks_impl(c, n_views, views, masks, sdf_out, false);
+}
+
+int vcb_carve_masks_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                           const uint8_t* const* masks_dev, float* const* sdf_out_dev) {
+  return carve_masks_impl(c, n_views, views, masks_dev, sdf_out_dev, true);
+}
+
+int vcb_carve_sdfs(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                   const float* const* sdfs) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (n_views < 0 || (n_views > 0 && (!views || !sdfs))) return fail(c, VCB_ERR_INVALID, "null argument");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  size_t max_pix = 0;
+  for (int i = 0; i < n_views; i++) {
+    if ((rc = check_view(c, views[i])) != VCB_OK) return rc;
+    if (!sdfs[i]) return fail(c, VCB_ERR_INVALID, "sdf %d is null", i);
+    max_pix = max(max_pix, (size_t)views[i].width * views[i].height);
+  }
+  if (n_views == 0) return VCB_OK;
+  if ((rc = ensure_pool(c, max_pix)) != VCB_OK) return rc;
+  float* pool = static_cast<float*>(c->pool.ptr);
+  float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
+  for (int i = 0; i < n_views; i++) {
+    const vcb_view& v = views[i];
+    const size_t pix = (size_t)v.width * v.height;
+    const int slot = c->pending;
+    float* dst = pool + (size_t)slot * c->slot_floats;
+    CU(c, cudaMemcpyAsync(dst, sdfs[i], pix * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    if (c->opt.update_outside == VCB_OUTSIDE_MAX) {  // voxel_carver.cc:436
+      Span span(c, 0);
+      launch_image_max(dst, (int64_t)pix, max_sdf + slot, c->stream, &c->stage_launches[0]);
+    }
+    fill_fuse_view(&c->fp.views[slot], v, dst, max_sdf + slot);
+    c->pending++;
+    if (c->pending == kMaxViewsPerLaunch) {
+      if ((rc = flush_pending(c)) != VCB_OK) return rc;
+    }
+  }
+  CU(c, cudaStreamSynchronize(c->stream));
+  return VCB_OK;
+}
+
+int vcb_carve_sdfs_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                          const float* const* sdfs_dev) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (n_views < 0 || (n_views > 0 && (!views || !sdfs_dev))) return fail(c, VCB_ERR_INVALID, "null argument");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  for (int i = 0; i < n_views; i++) {
+    if ((rc = check_view(c, views[i])) != VCB_OK) return rc;
+    if (!sdfs_dev[i]) return fail(c, VCB_ERR_INVALID, "sdf %d is null", i);
+  }
+  if ((rc = flush_pending(c)) != VCB_OK) return rc;
+  float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
+  for (int i = 0; i < n_views; i++) {
+    const vcb_view& v = views[i];
+    const int slot = c->pending;
+    if (c->opt.update_outside == VCB_OUTSIDE_MAX) {
+      Span span(c, 0);
+      launch_image_max(sdfs_dev[i], (int64_t)v.width * v.height, max_sdf + slot, c->stream,
+                       &c->stage_launches[0]);
+    }
+    fill_fuse_view(&c->fp.views[slot], v, sdfs_dev[i], max_sdf + slot);
+    c->pending++;
+    if (c->pending == kMaxViewsPerLaunch || i == n_views - 1) {
+      if ((rc = flush_pending(c)) != VCB_OK) return rc;
+    }
+  }
+  return VCB_OK;
+}
+
+static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width, int32_t height,
+                             const int32_t roi_min[2], const int32_t roi_max[2], int mode,
+                             int normalize, int truncate, float band, float* dist) {
+  if (!mask || !dist || !roi_min || !roi_max) return fail(nullptr, VCB_ERR_INVALID, "null argument");
+  vcb_view v;
+  memset(&v, 0, sizeof(v));
+  v.width = width;
+  v.height = height;
+  v.roi_min[0] = roi_min[0];
+  v.roi_min[1] = roi_min[1];
+  v.roi_max[0] = roi_max[0];
+  v.roi_max[1] = roi_max[1];
+  int rc = check_view(nullptr, v);
+  if (rc != VCB_OK) return rc;
+  if ((rc = use_device(nullptr, device)) != VCB_OK) return rc;
+  const size_t pix = (size_t)width * height;
+  Scratch buf;
+  // layout: float out | int16 rowd | int16 cold | mask | SdfView | int absmax | float max
+  const size_t off_rowd = pix * sizeof(float);
+  const size_t off_cold = off_rowd + pix * sizeof(int16_t);
+  const size_t off_mask = off_cold + pix * sizeof(int16_t);
+  const size_t off_view = (off_mask + pix + 255) / 256 * 256;
+  const size_t off_misc = off_view + 256;
+  CU(nullptr, buf.reserve(off_misc + 256));
+  char* base = static_cast<char*>(buf.ptr);
+  SdfView hv;
+  hv.mask = reinterpret_cast<uint8_t*>(base + off_mask);
+  hv.out = reinterpret_cast<float*>(base);
+  hv.rowd = reinterpret_cast<int16_t*>(base + off_rowd);
+  hv.cold = reinterpret_cast<int16_t*>(base + off_cold);
+  hv.absmax = reinterpret_cast<int*>(base + off_misc);
+  hv.max_out = reinterpret_cast<float*>(base + off_misc + 64);
+  hv.width = width;
+  hv.height = height;
+  hv.rx0 = roi_min[0];
+  hv.ry0 = roi_min[1];
+  hv.rx1 = roi_max[0];
+  hv.ry1 = roi_max[1];
+  cudaError_t e = cudaMemcpy(base + off_mask, mask, pix, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(base + off_view, &hv, sizeof(hv), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    launch_sdf2d(reinterpret_cast<SdfView*>(base + off_view), &hv, 1, mode, normalize, truncate,
+                 band, nullptr, nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(dist, base, pix * sizeof(float), cudaMemcpyDeviceToHost);
+  buf.release();
+  if (e != cudaSuccess) return fail(nullptr, VCB_ERR_CUDA, "2D SDF: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
+int vcb_distance_transform_l1(int32_t device, const uint8_t* mask, int32_t width, int32_t height,
+                              const int32_t roi_min[2], const int32_t roi_max[2], float* dist) {
+  return sdf_free_function(device, mask, width, height, roi_min, roi_max, kSdfDistanceL1, 0, 0,
+                           0.1f, dist);
+}
+
+int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t width,
+                                   int32_t height, const int32_t roi_min[2],
+                                   const int32_t roi_max[2], int32_t minmax_normalize,
+                                   int32_t use_truncation, float truncation_band, float* dist) {
+  return sdf_free_function(device, mask, width, height, roi_min, roi_max, kSdfSigned,
+                           minmax_normalize, use_truncation, truncation_band, dist);
+}
+
+int vcb_extract_iso_count(vcb_carver* c, double iso_level, int32_t linear_interp,
+                          int64_t* n_vertices, int64_t* n_faces) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = vcb_flush(c);
+  if (rc != VCB_OK) return rc;
+  {
+    Span span(c, 3);
+    cudaError_t e = iso_extract(grid_desc(c), c->un_implied, iso_level, linear_interp, &c->iso,
+                                c->stream, &c->stage_launches[3]);
+    if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "marching cubes: %s", cudaGetErrorString(e));
+  }
+  if (c->iso.n_vertices > INT32_MAX || c->iso.n_faces > INT32_MAX)
+    return fail(c, VCB_ERR_UNSUPPORTED, "mesh exceeds int32 indices (mesh.cc:241-271)");
+  if (n_vertices) *n_vertices = c->iso.n_vertices;
+  if (n_faces) *n_faces = c->iso.n_faces;
+  return VCB_OK;
+}
+
+int vcb_extract_iso_fill(vcb_carver* c, float* vertices, int32_t* faces) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (c->iso.n_vertices < 0) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_count has not run");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  if (vertices && c->iso.n_vertices > 0)
+    CU(c, cudaMemcpyAsync(vertices, c->iso.verts.ptr, (size_t)c->iso.n_vertices * 12,
+                          cudaMemcpyDeviceToHost, c->stream));
+  if (faces && c->iso.n_faces > 0)
+    CU(c, cudaMemcpyAsync(faces, c->iso.faces.ptr, (size_t)c->iso.n_faces * 12,
+                          cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return VCB_OK;
+}
+
+int vcb_extract_iso_device(vcb_carver* c, const float** vertices_dev, const int32_t** faces_dev) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (c->iso.n_vertices < 0) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_count has not run");
+  if (vertices_dev) *vertices_dev = static_cast<const float*>(c->iso.verts.ptr);
+  if (faces_dev) *faces_dev = static_cast<const int32_t*>(c->iso.faces.ptr);
+  return VCB_OK;
+}
+
+int vcb_extract_voxel_count(vcb_carver* c, int32_t inside_empty, int64_t* n_voxels) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = vcb_flush(c);
+  if (rc != VCB_OK) return rc;
+  if (inside_empty && c->z_begin > 0)
+    return fail(c, VCB_ERR_UNSUPPORTED, "inside_empty needs the plane below the slab (single-GPU only)");
+  {
+    Span span(c, 2);
+    cudaError_t e = voxel_extract_count(grid_desc(c), inside_empty, &c->vox, c->stream,
+                                        &c->stage_launches[2]);
+    if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "ExtractVoxel: %s", cudaGetErrorString(e));
+  }
+  if (n_voxels) *n_voxels = c->vox.n_voxels;
+  return VCB_OK;
+}
+
+int vcb_extract_voxel_fill(vcb_carver* c, float* vertices, int32_t* faces) {
+  if (!c || !vertices || !faces) return fail(c, VCB_ERR_INVALID, "null argument");
+  if (c->vox.n_voxels < 0) return fail(c, VCB_ERR_STATE, "vcb_extract_voxel_count has not run");
+  if (c->vox.n_voxels * 24 > INT32_MAX)
+    return fail(c, VCB_ERR_UNSUPPORTED, "voxel mesh exceeds int32 indices (mesh.cc:241-271)");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  Span span(c, 2);
+  cudaError_t e = voxel_extract_fill(grid_desc(c), &c->vox, vertices, faces, c->stream,
+                                     &c->stage_launches[2]);
+  if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "ExtractVoxel fill: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
+int vcb_extract_voxel_occupancy(vcb_carver* c, uint8_t* flags) {
+  if (!c || !flags) return fail(c, VCB_ERR_INVALID, "null argument");
+  if (c->vox.n_voxels < 0) return fail(c, VCB_ERR_STATE, "vcb_extract_voxel_count has not run");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  cudaError_t e = voxel_extract_flags(grid_desc(c), &c->vox, flags, c->stream,
+                                      &c->stage_launches[2]);
+  if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "occupancy: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
+int vcb_download_grid(vcb_carver* c, float* sdf, int32_t* update_num) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = vcb_flush(c);
+  if (rc != VCB_OK) return rc;
+  const size_t n = (size_t)slab_voxels(c);
+  if (sdf) CU(c, cudaMemcpyAsync(sdf, c->sdf, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+  if (update_num)
+    CU(c, cudaMemcpyAsync(update_num, c->un, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return VCB_OK;
+}
+
+int vcb_upload_grid(vcb_carver* c, const float* sdf, const int32_t* update_num) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = vcb_flush(c);
+  if (rc != VCB_OK) return rc;
+  const size_t n = (size_t)slab_voxels(c);
+  if (sdf) CU(c, cudaMemcpyAsync(c->sdf, sdf, n * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  if (update_num)
+    CU(c, cudaMemcpyAsync(c->un, update_num, n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  c->un_implied = false;  // arbitrary state: marching cubes must read update_num itself
+  return VCB_OK;
+}
+
+int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (sdf_dev) *sdf_dev = c->sdf;
+  if (update_num_dev) *update_num_dev = c->un;
+  return VCB_OK;
+}
+
+int vcb_stage_times(vcb_carver* c, float ms[4], int64_t launches[4]) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  resolve_spans(c);
+  for (int i = 0; i < 4; i++) {
+    if (ms) ms[i] = c->stage_ms[i];
+    if (launches) launches[i] = c->stage_launches[i];
+    c->stage_ms[i] = 0;
+    c->stage_launches[i] = 0;
+  }
+  return VCB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,121 @@
+// Internal declarations shared by the CUDA translation units of libvacancy_b200.so.
+// sm_100a only; compiled with -fmad=false so that no float/double multiply-add is ever contracted:
+// the reference is built for baseline x86-64 (one rounding per operation) and the fused grid must
+// reproduce it bit for bit.  Where an FMA is wanted it is written explicitly (__fmaf_rn).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/vacancy_b200.h"
+
+namespace vcb {
+
+constexpr float kInvalidSdf = -3.402823466e+38f;  // numeric_limits<float>::lowest(), voxel_carver.cc:100
+constexpr int kMaxViewsPerLaunch = 64;            // views fused per kernel launch
+constexpr int kSdfSubBatch = 8;                   // views per 2D-SDF kernel group (scratch stays L2-sized)
+constexpr int kSegVoxels = 32;                    // one extraction segment = 32 voxels along x
+constexpr int16_t kRowInf = 32767;                // "no opposite pixel" marker in the int16 passes
+constexpr int kMaxImageDim = 16384;               // keeps L1 distances < kRowInf
+
+// ---- per-view parameters of the fusion kernel (lives in the kernel parameter / constant bank) ----
+struct FuseView {
+  float m[12];         // w2c row-major 3x4
+  float fx, fy, cx, cy;
+  float roi_min_x, roi_min_y, roi_max_x, roi_max_y;  // ROI as float (compared against float coords)
+  int roi_min_xi, roi_min_yi, roi_max_xi, roi_max_yi;
+  int pitch;           // image width in pixels
+  int model;           // VCB_CAMERA_*
+  const float* image;  // device SDF image
+  const float* max_sdf;  // device scalar: max over the whole image (only read for VCB_OUTSIDE_MAX)
+};
+
+struct FuseParams {
+  float* sdf;            // slab state, plane z_begin first
+  int32_t* update_num;
+  const float* pos_x;    // global position tables (device)
+  const float* pos_y;
+  const float* pos_z;
+  const float2* wtab;    // weighted-average table: {w*float(n), 1/(w*float(n+1))}, n in [0, wtab_n)
+  int wtab_n;
+  int nx, ny;
+  int z_begin, z_end;    // owned planes
+  int n_views;
+  int max_update_num;
+  int use_truncation;
+  int update_outside;
+  float weight;
+  FuseView views[kMaxViewsPerLaunch];
+};
+
+// ---- per-view descriptor of the 2D SDF kernels (device array) ----
+struct SdfView {
+  const uint8_t* mask;   // device, width x height
+  float* out;            // device float image
+  int16_t* rowd;         // scratch: signed row distance
+  int16_t* cold;         // scratch: signed L1 distance
+  int* absmax;           // scratch: [0] max |D| over the ROI (INT_MAX when some pixel has no seed)
+  float* max_out;        // device scalar: max over the final float image
+  int width, height;
+  int rx0, ry0, rx1, ry1;
+};
+
+enum SdfMode { kSdfSigned = 0, kSdfDistanceL1 = 1 };
+
+void launch_sdf2d(const SdfView* views_dev, const SdfView* views_host, int n_views, int mode,
+                  int normalize, int truncate, float band, cudaStream_t stream, int64_t* launches);
+void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_t stream,
+                      int64_t* launches);
+void launch_fusion(const FuseParams& p, int interp, int update, cudaStream_t stream,
+                   int64_t* launches);
+
+// ---- extraction ----
+struct GridDesc {
+  const float* sdf;          // slab state (plane z_begin first)
+  const int32_t* update_num;
+  const float* pos_x;
+  const float* pos_y;
+  const float* pos_z;
+  int nx, ny, nz;            // GLOBAL dims
+  int z_begin, z_end;        // owned planes
+  int halo;                  // number of valid sdf planes stored below z_begin (0 or 2)
+  float resolution;
+};
+
+struct Scratch {  // grow-only device buffer
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  cudaError_t reserve(size_t n);
+  void release();
+};
+
+// exclusive prefix sum of n uint64 values (in -> out, may alias); *total_dev receives the sum
+cudaError_t scan_exclusive_u64(const uint64_t* in, uint64_t* out, int64_t n, uint64_t* total_dev,
+                               Scratch* tmp, cudaStream_t stream, int64_t* launches);
+
+struct VoxelExtract {  // state kept between _count and _fill
+  Scratch bits, segbase, tmp, stage;
+  int64_t n_voxels = -1;
+  int inside_empty = 0;
+};
+cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, VoxelExtract* st,
+                                cudaStream_t stream, int64_t* launches);
+cudaError_t voxel_extract_fill(const GridDesc& g, VoxelExtract* st, float* vertices_host,
+                               int32_t* faces_host, cudaStream_t stream, int64_t* launches);
+cudaError_t voxel_extract_flags(const GridDesc& g, VoxelExtract* st, uint8_t* flags_host,
+                                cudaStream_t stream, int64_t* launches);
+
+struct IsoExtract {
+  Scratch ibits, vbits, cbits, abits, segcnt, segbase, active, tmp, hkeys, hvals, verts, faces,
+      counters;
+  int64_t n_vertices = -1, n_faces = -1;
+};
+cudaError_t iso_extract(const GridDesc& g, bool un_implied, double iso_level, int linear_interp,
+                        IsoExtract* st, cudaStream_t stream, int64_t* launches);
+
+void init_mc_tables();  // uploads the constant-memory tables once per device
+
+}  // namespace vcb

@@ -1,0 +1,533 @@
+// K3 - marching cubes on the GPU with the reference's exact vertex numbering and face order.
+//
+// Replaces vacancy::MarchingCubes (marching_cubes.cc:63-228) and VertexInterp (:25-57).
+// The reference walks cubes in raster order (z, y, x; x fastest), each cube indexed by its MAX
+// corner voxel, and welds vertices through a std::map keyed by the edge's two voxel ids: a vertex is
+// numbered the first time any cube references its edge.  That sequential rule is restated
+// order-independently:
+//   * cube c is "non-skipped" iff update_num(c) >= 1 and none of its 8 corners holds kVal (:88-112);
+//   * the OWNER of a grid edge is the first non-skipped cube, in raster order, among the <= 4 cubes
+//     sharing it; every non-skipped cube that contains a crossed edge references it;
+//   * inside the owner the vertex takes the rank of its first reference in the triangle-table walk
+//     (i ascending, j = 0..2 reading tri[i + 2 - j], :199-218) among the edges the cube owns, and
+//     its position is VertexInterp evaluated with the owner's local edge direction;
+//   * vertex id = (exclusive prefix sum over raster order of owned-edge counts) + rank;
+//     face id   = (exclusive prefix sum of triangle counts) + position in the cube's list.
+//
+// Passes (S = segment of 32 cubes along x):
+//   mc_bits_kernel   dense, HBM-bound: reads each sdf value once (4 B/voxel), writes 2 bits/voxel:
+//                    I = (double)sdf < iso  (:121-128)   V = sdf != kVal (:103-112)
+//   mc_cube_kernel   bitmap-only (1/16 of the data): per S, word-parallel "all 8 corners valid" (C)
+//                    and "8 inside-bits not all equal" -> active-cube word A; compacts active S.
+//   mc_count_kernel  warp per active S: cube index, edge ownership, counts -> per-S (nv, nt).
+//   scan             exclusive prefix over S in raster order (extract_voxel.cu).
+//   mc_vertex_kernel warp per active S: owned vertices -> positions (float64 interpolation, :28-46),
+//                    written at their final index; edge -> vertex id goes into a hash table.
+//   mc_face_kernel   warp per active S: triangles in table order, ids looked up by edge key.
+// Algorithmic bytes: 4 B/voxel + 12 B/vertex + 12 B/face.
+#include <float.h>
+#include <math.h>
+
+#include "common.cuh"
+#include "mc_tables_packed.h"
+
+namespace vcb {
+
+namespace {
+
+__device__ uint64_t d_tri[256];       // packed triangle table, nibble i = edge of tri[i], 0xF = end
+__device__ uint16_t d_edge_mask[256]; // Bourke edgeTable, derived: edge flagged iff corners differ
+__device__ uint8_t d_ntri[256];
+
+// corner k -> offset from the cube's max corner (marching_cubes.cc:93-101)
+__constant__ signed char c_corner[8][3] = {{-1, -1, -1}, {0, -1, -1}, {0, 0, -1}, {-1, 0, -1},
+                                           {-1, -1, 0},  {0, -1, 0},  {0, 0, 0},  {-1, 0, 0}};
+// edge e -> (interpolate from corner, to corner) (marching_cubes.cc:138-197)
+__constant__ unsigned char c_edge_corner[12][2] = {{0, 1}, {1, 2}, {2, 3}, {3, 0}, {4, 5}, {5, 6},
+                                                   {6, 7}, {7, 4}, {0, 4}, {1, 5}, {2, 6}, {3, 7}};
+
+struct McGeom {
+  int nx, ny;
+  int spr;        // segments (words) per row
+  int zb;         // first stored plane (z_begin - halo)
+  int z_begin, z_end;
+  int cz0;        // first owned cube layer = max(1, z_begin)
+  int64_t n_words;   // spr * ny * stored planes
+  int64_t n_segs;    // spr * ny * owned planes
+};
+
+__host__ __device__ inline McGeom mc_geom(const GridDesc& g) {
+  McGeom m;
+  m.nx = g.nx;
+  m.ny = g.ny;
+  m.spr = (g.nx + 31) / 32;
+  m.zb = g.z_begin - g.halo;
+  m.z_begin = g.z_begin;
+  m.z_end = g.z_end;
+  m.cz0 = g.z_begin > 1 ? g.z_begin : 1;
+  m.n_words = (int64_t)m.spr * g.ny * (g.z_end - m.zb);
+  m.n_segs = (int64_t)m.spr * g.ny * (g.z_end - g.z_begin);
+  return m;
+}
+
+// word index in the stored-plane bitmaps / owned-plane segment arrays
+__device__ __forceinline__ int64_t word_index(const McGeom& m, int sx, int y, int z) {
+  return ((int64_t)(z - m.zb) * m.ny + y) * m.spr + sx;
+}
+__device__ __forceinline__ int64_t seg_index(const McGeom& m, int sx, int y, int z) {
+  return ((int64_t)(z - m.z_begin) * m.ny + y) * m.spr + sx;
+}
+__device__ __forceinline__ unsigned get_bit(const uint32_t* __restrict__ bits, const McGeom& m,
+                                            int x, int y, int z) {
+  return (bits[word_index(m, x >> 5, y, z)] >> (x & 31)) & 1u;
+}
+
+// ---- dense pass ---------------------------------------------------------------------------------
+constexpr int kBitsRows = 4;  // rows per block iteration: 4 independent loads in flight per thread
+
+__global__ void __launch_bounds__(256) mc_bits_kernel(const float* __restrict__ sdf_stored,
+                                                      int nx, int spr, int64_t n_rows, float thr,
+                                                      uint32_t* __restrict__ ibits,
+                                                      uint32_t* __restrict__ vbits) {
+  const int lane = threadIdx.x & 31;
+  const int warps = blockDim.x >> 5;
+  const int64_t row0 = (int64_t)blockIdx.x * kBitsRows;
+  for (int sx = threadIdx.x >> 5; sx < spr; sx += warps) {
+    const int x = sx * 32 + lane;
+    float s[kBitsRows];
+#pragma unroll
+    for (int r = 0; r < kBitsRows; r++) {
+      const int64_t row = row0 + r;
+      s[r] = (x < nx && row < n_rows) ? sdf_stored[row * nx + x] : kInvalidSdf;
+    }
+#pragma unroll
+    for (int r = 0; r < kBitsRows; r++) {
+      const int64_t row = row0 + r;
+      const bool valid = (x < nx) && (s[r] != kInvalidSdf);
+      const unsigned iw = __ballot_sync(0xffffffffu, valid && (s[r] < thr));
+      const unsigned vw = __ballot_sync(0xffffffffu, valid);
+      if (lane == 0 && row < n_rows) {
+        ibits[row * spr + sx] = iw;
+        vbits[row * spr + sx] = vw;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) mc_ubits_kernel(const int32_t* __restrict__ un, int nx,
+                                                       int spr, int64_t n_rows,
+                                                       uint32_t* __restrict__ ubits) {
+  const int lane = threadIdx.x & 31;
+  const int warps = blockDim.x >> 5;
+  const int64_t row = blockIdx.x;
+  for (int sx = threadIdx.x >> 5; sx < spr; sx += warps) {
+    const int x = sx * 32 + lane;
+    const bool u = (x < nx) && (un[row * nx + x] >= 1);
+    const unsigned w = __ballot_sync(0xffffffffu, u);
+    if (lane == 0) ubits[row * spr + sx] = w;
+  }
+}
+
+// ---- bitmap pass --------------------------------------------------------------------------------
+// pair word: bit i = b[x] & b[x-1]   /  any word: bit i = b[x] | b[x-1]
+__device__ __forceinline__ unsigned shift_in(unsigned w, unsigned prev) {
+  return (w << 1) | (prev >> 31);
+}
+
+__global__ void __launch_bounds__(256)
+    mc_cube_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
+                   const uint32_t* __restrict__ vbits, const uint32_t* __restrict__ ubits,
+                   uint32_t* __restrict__ cbits, uint32_t* __restrict__ abits,
+                   uint64_t* __restrict__ segcnt, uint32_t* __restrict__ active,
+                   unsigned* __restrict__ n_active) {
+  const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= m.n_words) return;
+  const int sx = (int)(w % m.spr);
+  const int64_t row = w / m.spr;
+  const int y = (int)(row % m.ny);
+  const int z = (int)(row / m.ny) + m.zb;
+  unsigned c = 0, a = 0;
+  if (y >= 1 && z >= 1 && z > m.zb) {
+    unsigned all_v = 0xffffffffu, all_i = 0xffffffffu, any_i = 0;
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      const int64_t wi = word_index(m, sx, y - (r & 1), z - (r >> 1));
+      const unsigned v = vbits[wi], i = ibits[wi];
+      const unsigned vp = sx > 0 ? vbits[wi - 1] : 0u, ip = sx > 0 ? ibits[wi - 1] : 0u;
+      all_v &= v & shift_in(v, vp);
+      all_i &= i & shift_in(i, ip);
+      any_i |= i | shift_in(i, ip);
+    }
+    c = all_v;  // x == 0 is excluded automatically: bit -1 shifts in as 0
+    if (ubits) c &= ubits[word_index(m, sx, y, z)];  // marching_cubes.cc:88-90
+    a = c & any_i & ~all_i;
+  }
+  cbits[w] = c;
+  if (z >= m.z_begin) {
+    const int64_t seg = seg_index(m, sx, y, z);
+    abits[seg] = a;
+    segcnt[seg] = 0;
+    if (a) active[atomicAdd(n_active, 1u)] = (uint32_t)seg;
+  }
+}
+
+// ---- per-cube analysis --------------------------------------------------------------------------
+struct CubeInfo {
+  int ci;          // cube index, marching_cubes.cc:121-128
+  unsigned owned;  // crossed edges whose vertex this cube creates
+};
+
+__device__ __forceinline__ unsigned cube_ok(const uint32_t* __restrict__ cbits, const McGeom& m,
+                                            int x, int y, int z) {
+  if (x < 1 || x >= m.nx || y < 1 || y >= m.ny || z < 1 || z <= m.zb) return 0u;
+  return get_bit(cbits, m, x, y, z);
+}
+
+__device__ __forceinline__ CubeInfo cube_info(const McGeom& m, const uint32_t* __restrict__ ibits,
+                                              const uint32_t* __restrict__ cbits, int x, int y,
+                                              int z) {
+  CubeInfo info;
+  int ci = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    ci |= (int)get_bit(ibits, m, x + c_corner[k][0], y + c_corner[k][1], z + c_corner[k][2]) << k;
+  }
+  info.ci = ci;
+  // earlier cubes (raster order) that share an edge with this one
+  const unsigned n1 = cube_ok(cbits, m, x, y - 1, z - 1), n2 = cube_ok(cbits, m, x, y, z - 1);
+  const unsigned n3 = cube_ok(cbits, m, x, y + 1, z - 1), n4 = cube_ok(cbits, m, x - 1, y, z - 1);
+  const unsigned n5 = cube_ok(cbits, m, x + 1, y, z - 1), n6 = cube_ok(cbits, m, x, y - 1, z);
+  const unsigned n7 = cube_ok(cbits, m, x - 1, y, z), n8 = cube_ok(cbits, m, x - 1, y - 1, z);
+  const unsigned n9 = cube_ok(cbits, m, x + 1, y - 1, z);
+  unsigned taken = 0;  // edges already created by an earlier cube
+  taken |= (n1 | n2 | n6) << 0;
+  taken |= (n2 | n5) << 1;
+  taken |= (n2 | n3) << 2;
+  taken |= (n4 | n2 | n7) << 3;
+  taken |= (n6) << 4;
+  taken |= (n7) << 7;
+  taken |= (n8 | n6 | n7) << 8;
+  taken |= (n6 | n9) << 9;
+  taken |= (n7) << 11;
+  info.owned = d_edge_mask[ci] & ~taken;
+  return info;
+}
+
+// canonical edge key: (lower voxel id, axis)
+__device__ __forceinline__ uint64_t edge_key(const McGeom& m, int x, int y, int z, int e) {
+  const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
+  const int xa = x + c_corner[a][0], ya = y + c_corner[a][1], za = z + c_corner[a][2];
+  const int xb = x + c_corner[b][0], yb = y + c_corner[b][1], zb = z + c_corner[b][2];
+  const int lx = min(xa, xb), ly = min(ya, yb), lz = min(za, zb);
+  const int axis = (xa != xb) ? 0 : ((ya != yb) ? 1 : 2);
+  const uint64_t id = ((uint64_t)lz * m.ny + ly) * m.nx + lx;
+  return (id << 2) | (uint64_t)axis;
+}
+
+constexpr uint64_t kEmptyKey = 0xffffffffffffffffull;
+
+__device__ __forceinline__ uint64_t hash_slot(uint64_t key, uint64_t mask) {
+  key *= 0x9E3779B97F4A7C15ull;
+  return (key >> 20) & mask;
+}
+
+__device__ __forceinline__ void hash_insert(uint64_t* keys, int32_t* vals, uint64_t mask,
+                                            uint64_t key, int32_t val) {
+  uint64_t slot = hash_slot(key, mask);
+  while (true) {
+    const unsigned long long prev =
+        atomicCAS(reinterpret_cast<unsigned long long*>(keys + slot), kEmptyKey, key);
+    if (prev == kEmptyKey || prev == key) {
+      vals[slot] = val;
+      return;
+    }
+    slot = (slot + 1) & mask;
+  }
+}
+
+__device__ __forceinline__ int32_t hash_find(const uint64_t* __restrict__ keys,
+                                             const int32_t* __restrict__ vals, uint64_t mask,
+                                             uint64_t key) {
+  uint64_t slot = hash_slot(key, mask);
+  while (true) {
+    const uint64_t k = keys[slot];
+    if (k == key) return vals[slot];
+    if (k == kEmptyKey) return -1;
+    slot = (slot + 1) & mask;
+  }
+}
+
+__device__ __forceinline__ void seg_coords(const McGeom& m, int64_t seg, int* sx, int* y, int* z) {
+  *sx = (int)(seg % m.spr);
+  const int64_t row = seg / m.spr;
+  *y = (int)(row % m.ny);
+  *z = (int)(row / m.ny) + m.z_begin;
+}
+
+__global__ void __launch_bounds__(128)
+    mc_count_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
+                    const uint32_t* __restrict__ cbits, const uint32_t* __restrict__ abits,
+                    const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
+                    uint64_t* __restrict__ segcnt) {
+  const int lane = threadIdx.x & 31;
+  const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (wid >= *n_active) return;
+  const int64_t seg = active[wid];
+  int sx, y, z;
+  seg_coords(m, seg, &sx, &y, &z);
+  unsigned nv = 0, nt = 0;
+  if ((abits[seg] >> lane) & 1u) {
+    const CubeInfo info = cube_info(m, ibits, cbits, sx * 32 + lane, y, z);
+    nv = __popc(info.owned);
+    nt = d_ntri[info.ci];
+  }
+  nv = __reduce_add_sync(0xffffffffu, nv);
+  nt = __reduce_add_sync(0xffffffffu, nt);
+  if (lane == 0) segcnt[seg] = ((uint64_t)nv << 32) | nt;
+}
+
+// marching_cubes.cc:25-47, float64, one rounding per operation
+__device__ __forceinline__ void vertex_interp(double iso, const float p1[3], const float p2[3],
+                                              double v1, double v2, float out[3]) {
+  if (fabs(iso - v1) < 0.00001) {
+    out[0] = p1[0]; out[1] = p1[1]; out[2] = p1[2];
+    return;
+  }
+  if (fabs(iso - v2) < 0.00001) {
+    out[0] = p2[0]; out[1] = p2[1]; out[2] = p2[2];
+    return;
+  }
+  if (fabs(v1 - v2) < 0.00001) {
+    out[0] = p1[0]; out[1] = p1[1]; out[2] = p1[2];
+    return;
+  }
+  const double mu = __ddiv_rn(__dsub_rn(iso, v1), __dsub_rn(v2, v1));
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    const double d = __dsub_rn((double)p2[a], (double)p1[a]);
+    out[a] = (float)__dadd_rn((double)p1[a], __dmul_rn(mu, d));
+  }
+}
+
+__global__ void __launch_bounds__(128)
+    mc_vertex_kernel(const McGeom m, const GridDesc g, const uint32_t* __restrict__ ibits,
+                     const uint32_t* __restrict__ cbits, const uint32_t* __restrict__ abits,
+                     const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
+                     const uint64_t* __restrict__ segbase, double iso, int linear_interp,
+                     int64_t vertex_offset, float* __restrict__ vertices, uint64_t* hkeys,
+                     int32_t* hvals, uint64_t hmask) {
+  const int lane = threadIdx.x & 31;
+  const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (wid >= *n_active) return;
+  const int64_t seg = active[wid];
+  int sx, y, z;
+  seg_coords(m, seg, &sx, &y, &z);
+  const int x = sx * 32 + lane;
+  const bool act = (abits[seg] >> lane) & 1u;
+  CubeInfo info;
+  info.ci = 0;
+  info.owned = 0;
+  if (act) info = cube_info(m, ibits, cbits, x, y, z);
+  const unsigned nv = __popc(info.owned);
+  unsigned inc = nv;
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (nv == 0) return;
+  int64_t vid = (int64_t)(segbase[seg] >> 32) + (inc - nv);
+  // corner values and positions
+  const size_t plane = (size_t)m.nx * m.ny;
+  float val[8], pos[8][3];
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const int cx = x + c_corner[k][0], cy = y + c_corner[k][1], cz = z + c_corner[k][2];
+    // g.sdf points at plane z_begin; halo planes sit at negative offsets
+    val[k] = g.sdf[((ptrdiff_t)cz - g.z_begin) * (ptrdiff_t)plane + (ptrdiff_t)cy * m.nx + cx];
+    pos[k][0] = g.pos_x[cx];
+    pos[k][1] = g.pos_y[cy];
+    pos[k][2] = g.pos_z[cz];
+  }
+  const uint64_t tri = d_tri[info.ci];
+  unsigned seen = 0;
+  for (int i = 0; i < 15 && ((tri >> (4 * i)) & 0xF) != 0xF; i += 3) {
+    for (int j = 0; j < 3; j++) {
+      const int e = (int)((tri >> (4 * (i + 2 - j))) & 0xF);
+      if ((seen >> e) & 1u) continue;
+      seen |= 1u << e;
+      if (!((info.owned >> e) & 1u)) continue;
+      const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
+      float p[3];
+      if (linear_interp) {
+        vertex_interp(iso, pos[a], pos[b], (double)val[a], (double)val[b], p);
+      } else {  // marching_cubes.cc:55
+        p[0] = pos[a][0]; p[1] = pos[a][1]; p[2] = pos[a][2];
+      }
+      vertices[vid * 3 + 0] = p[0];
+      vertices[vid * 3 + 1] = p[1];
+      vertices[vid * 3 + 2] = p[2];
+      hash_insert(hkeys, hvals, hmask, edge_key(m, x, y, z, e), (int32_t)(vid + vertex_offset));
+      vid++;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128)
+    mc_face_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
+                   const uint32_t* __restrict__ abits, const uint32_t* __restrict__ active,
+                   const unsigned* __restrict__ n_active, const uint64_t* __restrict__ segbase,
+                   int32_t* __restrict__ faces, const uint64_t* __restrict__ hkeys,
+                   const int32_t* __restrict__ hvals, uint64_t hmask) {
+  const int lane = threadIdx.x & 31;
+  const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (wid >= *n_active) return;
+  const int64_t seg = active[wid];
+  int sx, y, z;
+  seg_coords(m, seg, &sx, &y, &z);
+  const int x = sx * 32 + lane;
+  const bool act = (abits[seg] >> lane) & 1u;
+  int ci = 0;
+  if (act) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      ci |= (int)get_bit(ibits, m, x + c_corner[k][0], y + c_corner[k][1], z + c_corner[k][2]) << k;
+    }
+  }
+  const unsigned nt = act ? d_ntri[ci] : 0;
+  unsigned inc = nt;
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (nt == 0) return;
+  int64_t fid = (int64_t)(segbase[seg] & 0xffffffffull) + (inc - nt);
+  const uint64_t tri = d_tri[ci];
+  for (unsigned t = 0; t < nt; t++) {
+#pragma unroll
+    for (int j = 0; j < 3; j++) {  // face[j] = vertex of edge tri[i + (2 - j)], :202-204
+      const int e = (int)((tri >> (4 * (3 * t + 2 - j))) & 0xF);
+      faces[fid * 3 + j] = hash_find(hkeys, hvals, hmask, edge_key(m, x, y, z, e));
+    }
+    fid++;
+  }
+}
+
+const uint64_t h_tri[256] = VCB_MC_TRI_PACKED_INIT;
+const unsigned char h_edge_corner[12][2] = {{0, 1}, {1, 2}, {2, 3}, {3, 0}, {4, 5}, {5, 6},
+                                            {6, 7}, {7, 4}, {0, 4}, {1, 5}, {2, 6}, {3, 7}};
+
+}  // namespace
+
+void init_mc_tables() {
+  uint16_t em[256];
+  uint8_t nt[256];
+  for (int c = 0; c < 256; c++) {
+    int mask = 0;
+    for (int e = 0; e < 12; e++) {
+      const int a = (c >> h_edge_corner[e][0]) & 1, b = (c >> h_edge_corner[e][1]) & 1;
+      if (a != b) mask |= 1 << e;
+    }
+    em[c] = (uint16_t)mask;
+    int n = 0;
+    while (n < 5 && ((h_tri[c] >> (12 * n)) & 0xF) != 0xF) n++;
+    nt[c] = (uint8_t)n;
+  }
+  cudaMemcpyToSymbol(d_tri, h_tri, sizeof(h_tri));
+  cudaMemcpyToSymbol(d_edge_mask, em, sizeof(em));
+  cudaMemcpyToSymbol(d_ntri, nt, sizeof(nt));
+}
+
+// smallest float t with (double)s < iso  <=>  s < t for every float s
+static float iso_threshold(double iso) {
+  if (iso != iso) return NAN;
+  float t = (float)iso;                         // round to nearest
+  if ((double)t < iso) t = nextafterf(t, INFINITY);  // round up
+  return t;
+}
+
+cudaError_t iso_extract(const GridDesc& g, bool un_implied, double iso_level, int linear_interp,
+                        IsoExtract* st, cudaStream_t stream, int64_t* launches) {
+  const McGeom m = mc_geom(g);
+  st->n_vertices = st->n_faces = -1;
+  if (m.n_segs >= (int64_t)0xffffffffll) return cudaErrorInvalidValue;
+  cudaError_t e;
+#define VCB_TRY(x) \
+  if ((e = (x)) != cudaSuccess) return e
+  const size_t wbytes = (size_t)m.n_words * sizeof(uint32_t);
+  VCB_TRY(st->ibits.reserve(wbytes));
+  VCB_TRY(st->vbits.reserve(wbytes));
+  VCB_TRY(st->cbits.reserve(wbytes));
+  VCB_TRY(st->abits.reserve((size_t)m.n_segs * sizeof(uint32_t)));
+  VCB_TRY(st->segcnt.reserve((size_t)(m.n_segs + 1) * sizeof(uint64_t)));
+  VCB_TRY(st->segbase.reserve((size_t)(m.n_segs + 1) * sizeof(uint64_t)));
+  VCB_TRY(st->active.reserve((size_t)m.n_segs * sizeof(uint32_t)));
+  VCB_TRY(st->counters.reserve(256));
+  uint32_t* ibits = static_cast<uint32_t*>(st->ibits.ptr);
+  uint32_t* vbits = static_cast<uint32_t*>(st->vbits.ptr);
+  uint32_t* cbits = static_cast<uint32_t*>(st->cbits.ptr);
+  uint32_t* abits = static_cast<uint32_t*>(st->abits.ptr);
+  uint64_t* segcnt = static_cast<uint64_t*>(st->segcnt.ptr);
+  uint64_t* segbase = static_cast<uint64_t*>(st->segbase.ptr);
+  uint32_t* active = static_cast<uint32_t*>(st->active.ptr);
+  unsigned* n_active = static_cast<unsigned*>(st->counters.ptr);
+  uint32_t* ubits = nullptr;
+
+  const size_t plane = (size_t)g.nx * g.ny;
+  const float* sdf_stored = g.sdf - (ptrdiff_t)g.halo * (ptrdiff_t)plane;
+  const int64_t n_rows = (int64_t)g.ny * (g.z_end - m.zb);
+  VCB_TRY(cudaMemsetAsync(n_active, 0, sizeof(unsigned), stream));
+  mc_bits_kernel<<<(unsigned)((n_rows + kBitsRows - 1) / kBitsRows), 256, 0, stream>>>(
+      sdf_stored, g.nx, m.spr, n_rows, iso_threshold(iso_level), ibits, vbits);
+  if (launches) *launches += 1;
+  if (!un_implied) {
+    if (g.halo != 0) return cudaErrorInvalidValue;  // update_num has no halo planes
+    VCB_TRY(st->tmp.reserve(wbytes));
+    ubits = static_cast<uint32_t*>(st->tmp.ptr);
+    mc_ubits_kernel<<<(unsigned)n_rows, 256, 0, stream>>>(g.update_num, g.nx, m.spr, n_rows, ubits);
+    if (launches) *launches += 1;
+  }
+  mc_cube_kernel<<<(unsigned)((m.n_words + 255) / 256), 256, 0, stream>>>(
+      m, ibits, vbits, ubits, cbits, abits, segcnt, active, n_active);
+  if (launches) *launches += 1;
+  unsigned h_active = 0;
+  VCB_TRY(cudaMemcpyAsync(&h_active, n_active, sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
+  VCB_TRY(cudaStreamSynchronize(stream));
+  const unsigned wblocks = (h_active + 3) / 4;  // 4 warps per block
+  if (h_active > 0) {
+    mc_count_kernel<<<wblocks, 128, 0, stream>>>(m, ibits, cbits, abits, active, n_active, segcnt);
+    if (launches) *launches += 1;
+  }
+  // the ubits scratch (st->tmp) is dead from here on; the scan reuses st->tmp
+  VCB_TRY(scan_exclusive_u64(segcnt, segbase, m.n_segs, segbase + m.n_segs, &st->tmp, stream,
+                             launches));
+  uint64_t total = 0;
+  VCB_TRY(cudaMemcpyAsync(&total, segbase + m.n_segs, sizeof(total), cudaMemcpyDeviceToHost,
+                          stream));
+  VCB_TRY(cudaStreamSynchronize(stream));
+  const int64_t nv = (int64_t)(total >> 32), nf = (int64_t)(total & 0xffffffffull);
+  if (nv > 0) {
+    uint64_t cap = 1024;
+    while (cap < (uint64_t)nv * 2) cap <<= 1;
+    VCB_TRY(st->hkeys.reserve(cap * sizeof(uint64_t)));
+    VCB_TRY(st->hvals.reserve(cap * sizeof(int32_t)));
+    VCB_TRY(st->verts.reserve((size_t)nv * 3 * sizeof(float)));
+    VCB_TRY(st->faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int32_t)));
+    VCB_TRY(cudaMemsetAsync(st->hkeys.ptr, 0xff, cap * sizeof(uint64_t), stream));
+    mc_vertex_kernel<<<wblocks, 128, 0, stream>>>(
+        m, g, ibits, cbits, abits, active, n_active, segbase, iso_level, linear_interp, 0,
+        static_cast<float*>(st->verts.ptr), static_cast<uint64_t*>(st->hkeys.ptr),
+        static_cast<int32_t*>(st->hvals.ptr), cap - 1);
+    mc_face_kernel<<<wblocks, 128, 0, stream>>>(
+        m, ibits, abits, active, n_active, segbase, static_cast<int32_t*>(st->faces.ptr),
+        static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), cap - 1);
+    if (launches) *launches += 2;
+  }
+#undef VCB_TRY
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  st->n_vertices = nv;
+  st->n_faces = nf;
+  return cudaSuccess;
+}
+
+}  // namespace vcb
