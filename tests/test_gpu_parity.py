@@ -1,0 +1,258 @@
+"""GPU parity tests: every result of the CUDA path, obtained through the C ABI, is compared with
+the oracle (plain-C restatement; plus the compiled reference when oracle/_ref travelled along) on
+the same inputs.  Bar: BIT-EXACT for the 2D SDF, the fused grid, occupancy and mesh indices;
+mesh vertices bit-exact as well (north_star only asks for 1e-5 of the bbox diagonal)."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from oracle import bindings as B
+from tests import helpers as H
+from vacancy_b200 import (VoxelCarver, distance_transform_l1, make_signed_distance_field,
+                          synthetic as S)
+
+pytestmark = pytest.mark.gpu
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+
+
+def bits_equal(a, b):
+    return np.array_equal(np.ascontiguousarray(a).view(np.uint32),
+                          np.ascontiguousarray(b).view(np.uint32))
+
+
+def make_carver(opt):
+    car = VoxelCarver(H.product_options(opt))
+    assert car.Init(), car.last_error
+    return car
+
+
+# ---- K0: 2D SDF ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind", ["blobs", "noise", "grey", "full", "empty"])
+def test_sdf2d_fuzz(cuda_lib, port, kind):
+    rng = np.random.default_rng(hash(kind) % 1000 + 1)
+    for t in range(10):
+        h, w = int(rng.integers(1, 150)), int(rng.integers(1, 150))
+        mask = H.random_mask(rng, h, w, kind)
+        roi = None
+        if t % 3 == 1:
+            x0, y0 = int(rng.integers(0, w)), int(rng.integers(0, h))
+            roi = (x0, y0, int(rng.integers(x0, w)), int(rng.integers(y0, h)))
+        rmin, rmax = (roi[:2], roi[2:]) if roi else (None, None)
+        assert bits_equal(distance_transform_l1(mask, rmin, rmax),
+                          port.distance_transform_l1(mask, roi)), (kind, t, "dt")
+        for norm in (True, False):
+            for trunc in (True, False):
+                got = make_signed_distance_field(mask, rmin, rmax, norm, trunc, 0.1)
+                want = port.make_sdf(mask, roi, norm, trunc, 0.1)
+                assert bits_equal(got, want), (kind, t, norm, trunc, h, w, roi)
+
+
+def test_sdf2d_bunny_and_large(cuda_lib, port, bunny):
+    for i in range(6):
+        got = make_signed_distance_field(bunny.masks[i])
+        assert sha(got) == bunny.golden["modes"]["max"]["views"][i]["sdf2d"]["sha"]
+    # widths that are not multiples of 32, more than one block of row segments
+    cam = S.circle_cameras(3, 1000)[1]
+    mask = S.silhouette(cam, S.DUMBBELL)[:777, :]
+    for trunc in (False, True):
+        assert bits_equal(make_signed_distance_field(mask, use_truncation=trunc),
+                          port.make_sdf(mask, None, True, trunc, 0.1))
+
+
+# ---- K1 + K2 + K3 on the bundled bunny (config 1) -----------------------------------------------
+@pytest.mark.parametrize("mode", ["max", "tsdf"])
+def test_bunny_view_by_view(cuda_lib, bunny, mode):
+    """examples.cc's loop: carve one view, extract voxel + both iso surfaces, repeat."""
+    opt = H.oracle_options(bunny.bb_min, bunny.bb_max, H.BUNNY_RESOLUTION, **H.MODES[mode])
+    car = make_carver(opt)
+    assert list(car.dims) == bunny.golden["dims"]
+    rows = bunny.golden["modes"][mode]["views"]
+    for i in range(6):
+        cam = H.product_camera(H.bunny_camera(bunny, i), bunny.w2c[i])
+        ok, img = car.Carve(cam, bunny.masks[i], return_sdf=True)
+        assert ok
+        want = rows[i]
+        assert sha(img) == want["sdf2d"]["sha"]
+        sdf, un = car.download_grid()
+        assert sha(un) == want["un_sha"], i
+        assert sha(sdf) == want["sdf_sha"], i
+        v, f = car.ExtractIsoSurface(0.0, True)
+        assert [len(v), len(f)] == want["mc"]
+        assert [sha(v), sha(f)] == want["mc_sha"], i
+        assert car.ExtractVoxel(False, copy=False) == want["voxel_cubes"]
+        assert car.ExtractVoxel(True, copy=False) == want["surface_cubes"]
+    for key, want in bunny.golden["modes"][mode]["extra"].items():
+        iso, interp = key[3:].split("_interp")
+        v, f = car.ExtractIsoSurface(float(iso), bool(int(interp)))
+        assert [len(v), len(f), sha(v), sha(f)] == want, key
+    v, f = car.ExtractIsoSurface(0.0, True)
+    assert bits_equal(v, bunny.final[mode + "_verts"]) and np.array_equal(f, bunny.final[mode + "_faces"])
+
+
+def test_bunny_batched_equals_sequential(cuda_lib, bunny):
+    """All six views in ONE C-ABI call (one fused launch) give the same grid as six calls."""
+    opt = H.oracle_options(bunny.bb_min, bunny.bb_max, H.BUNNY_RESOLUTION, **H.MODES["tsdf"])
+    car = make_carver(opt)
+    cams = [H.product_camera(H.bunny_camera(bunny, i), bunny.w2c[i]) for i in range(6)]
+    ok, sdfs = car.carve_batch(cams, list(bunny.masks), return_sdf=True)
+    assert ok
+    sdf, un = car.download_grid()
+    assert bits_equal(sdf, bunny.final["tsdf_sdf"]) and np.array_equal(un, bunny.final["tsdf_un"])
+    # feeding the returned float SDFs through the Image1f overload reproduces it again
+    car2 = make_carver(opt)
+    for cam, img in zip(cams, sdfs):
+        assert car2.Carve(cam, img)
+    sdf2, un2 = car2.download_grid()
+    assert bits_equal(sdf2, sdf) and np.array_equal(un2, un)
+
+
+# ---- synthetic scenes, every option combination ---------------------------------------------------
+@pytest.mark.parametrize("cfg", [
+    dict(update=0, interp=1), dict(update=0, interp=0), dict(update=1, interp=1, truncation=True),
+    dict(update=1, interp=1, truncation=True, weight=0.7, max_update_num=3),
+    dict(update=0, interp=1, outside=1), dict(update=1, interp=0, outside=1, normalize=False),
+])
+def test_options_matrix(cuda_lib, port, cfg):
+    o = S.grid_option(40)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, **cfg)
+    car, orc = make_carver(opt), port.carver(opt)
+    assert tuple(car.dims) == tuple(orc.dims)
+    for a, b in zip(car.positions(), orc.positions()):
+        assert bits_equal(a, b)
+    pcams = S.circle_cameras(9, 200, tilt=0.5)
+    masks = [S.silhouette(c, S.DUMBBELL) for c in pcams]
+    ocams = [H.to_oracle_camera(c) for c in pcams]
+    ortho_c2w = np.eye(4)
+    ortho_c2w[:3, 3] = (-0.9, -0.8, -3.0)
+    ocams.append(B.Camera(200, 200, ortho_c2w, model=1))
+    pcams.append(H.product_camera(ocams[-1]))
+    masks.append(np.zeros((200, 200), np.uint8))
+    masks[-1][:2, :2] = 255
+    for i, (pc, oc, mask) in enumerate(zip(pcams, ocams, masks)):
+        roi = (7, 5, 190, 180) if i == 2 else None
+        kw = dict(roi_min=roi[:2], roi_max=roi[2:]) if roi else {}
+        ok, got = car.Carve(pc, mask, return_sdf=True, **kw)
+        want = orc.carve_mask(oc, mask, roi)
+        assert ok and bits_equal(got, want), i
+    (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+    assert np.array_equal(gn, wn)
+    assert bits_equal(gs, ws)
+    for iso, interp in ((0.0, True), (0.0, False), (0.03, True)):
+        H.assert_mesh_equal(car.ExtractIsoSurface(iso, interp), orc.extract_iso(iso, interp),
+                            o.bb_min, o.bb_max)
+    for inside_empty in (False, True):
+        flags, n = car.occupancy(inside_empty)
+        wflags, wn_ = orc.occupancy(inside_empty)
+        assert n == wn_ and np.array_equal(flags, wflags)
+        gv, gf = car.ExtractVoxel(inside_empty)
+        wv, wf = orc.extract_voxel(inside_empty)
+        assert np.array_equal(gf, wf) and bits_equal(gv, wv)
+
+
+def test_synthetic_golden_counts(cuda_lib):
+    """Counts recorded from the compiled reference (tests/golden/synth_golden.json)."""
+    want_all = H.load_synth_golden()
+    for name, n, views, size, weighted, shape in (
+            ("sphere32_max", 32, 6, 128, False, S.SPHERE),
+            ("dumbbell48_tsdf", 48, 10, 160, True, S.DUMBBELL),
+            ("dumbbell64_max", 64, 12, 256, False, S.DUMBBELL)):
+        want = want_all[name]
+        car = VoxelCarver(S.grid_option(n, weighted=weighted))
+        assert car.Init()
+        cams = S.circle_cameras(views, size, tilt=0.4)
+        assert car.carve_batch(cams, [S.silhouette(c, shape) for c in cams])
+        sdf, un = car.download_grid()
+        assert sha(sdf) == want["sdf_sha"] and sha(un) == want["un_sha"], name
+        v, f = car.ExtractIsoSurface(0.0, True)
+        assert [len(v), len(f)] == want["mc"] and [sha(v), sha(f)] == want["mc_sha"], name
+        assert car.ExtractVoxel(False, copy=False) == want["voxel_cubes"]
+        assert car.ExtractVoxel(True, copy=False) == want["surface_cubes"]
+
+
+def test_more_views_than_one_launch_and_update_cap(cuda_lib, port):
+    """150 views > 64 per launch; voxel_max_update_num = 40 makes the `update_num > max` gate
+    (voxel_carver.cc:447-450) bite in weighted mode; mixed image sizes in one batch."""
+    o = S.grid_option(32, weighted=True, max_update_num=40)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True,
+                         max_update_num=40)
+    car, orc = make_carver(opt), port.carver(opt)
+    cams = S.circle_cameras(75, 96, tilt=0.3) + S.circle_cameras(75, 128, tilt=-0.2)
+    masks = [S.silhouette(c, S.DUMBBELL) for c in cams]
+    assert car.carve_batch(cams, masks)
+    for c, m in zip(cams, masks):
+        orc.carve_mask(H.to_oracle_camera(c), m)
+    (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+    assert gn.max() == 41 and np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(car.ExtractIsoSurface(), orc.extract_iso(), o.bb_min, o.bb_max)
+
+
+def test_marching_cubes_handmade_grids(cuda_lib, port):
+    """Arbitrary uploaded states: skipped cubes, kVal corners, near-iso values, non-multiple-of-32
+    rows - the ownership / numbering rule away from the easy interior."""
+    rng = np.random.default_rng(11)
+    for bb_max, res in (((1.3, 1.1, 0.9), 0.1), ((7.0, 0.5, 0.45), 0.1), ((0.25, 0.25, 6.7), 0.1)):
+        opt = B.make_options((0, 0, 0), bb_max, res)
+        car, orc = make_carver(opt), port.carver(opt)
+        kval = port.invalid_sdf()
+        for t in range(5):
+            sdf = rng.normal(size=orc.count).astype(np.float32)
+            un = rng.integers(0, 3, orc.count).astype(np.int32)
+            sdf[rng.random(orc.count) < 0.15] = kval
+            sdf[rng.random(orc.count) < 0.05] = np.float32(1e-6) * rng.integers(-3, 4)
+            if t == 0:
+                un[:] = 1
+            car.upload_grid(sdf, un)
+            orc.upload(sdf, un)
+            for iso, interp in ((0.0, True), (0.25, True), (0.0, False)):
+                H.assert_mesh_equal(car.ExtractIsoSurface(iso, interp),
+                                    orc.extract_iso(iso, interp), (0, 0, 0), bb_max)
+            for inside_empty in (False, True):
+                flags, n = car.occupancy(inside_empty)
+                wflags, wn = orc.occupancy(inside_empty)
+                assert n == wn and np.array_equal(flags, wflags)
+
+
+def test_empty_and_degenerate(cuda_lib, port):
+    o = S.grid_option(16)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution)
+    car, orc = make_carver(opt), port.carver(opt)
+    # nothing carved yet: empty meshes, no cubes
+    v, f = car.ExtractIsoSurface()
+    assert v.shape == (0, 3) and f.shape == (0, 3)
+    assert car.ExtractVoxel(copy=False) == 0
+    # Carve before Init returns False like the shim of a null grid
+    fresh = VoxelCarver(H.product_options(opt))
+    assert fresh.Carve(S.circle_cameras(1, 32)[0], np.zeros((32, 32), np.uint8)) is False
+    # all-background and all-foreground silhouettes (FLT_MAX distances, voxel_carver.cc:107-114)
+    cam = S.circle_cameras(2, 64)[0]
+    for val in (0, 255):
+        mask = np.full((64, 64), val, np.uint8)
+        ok, got = car.Carve(cam, mask, return_sdf=True)
+        want = orc.carve_mask(H.to_oracle_camera(cam), mask)
+        assert ok and bits_equal(got, want)
+    (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+
+
+def test_against_compiled_reference(cuda_lib, ref):
+    """Same scenario through the UNMODIFIED reference (oracle/_ref) when it travelled along."""
+    o = S.grid_option(48, weighted=True)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True)
+    car, rc = make_carver(opt), ref.carver(opt)
+    cams = S.circle_cameras(8, 160, tilt=0.4)
+    for c in cams:
+        m = S.silhouette(c, S.DUMBBELL)
+        ok, got = car.Carve(c, m, return_sdf=True)
+        want = rc.carve_mask(H.to_oracle_camera(c), m)
+        assert ok and bits_equal(got, want)
+    (gs, gn), (ws, wn) = car.download_grid(), rc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(car.ExtractIsoSurface(), rc.extract_iso(), o.bb_min, o.bb_max)
+    gv, gf = car.ExtractVoxel()
+    wv, wf = rc.extract_voxel()
+    assert np.array_equal(gf, wf)
+    assert np.abs(gv - wv).max() <= 1e-5 * np.linalg.norm(np.array(o.bb_max) - o.bb_min)
