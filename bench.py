@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""Benchmark of the carving hot path (BASELINE.json metric: Gvoxel-view updates/s for carving plus
+marching-cubes ms at 1024^3).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg4]
+
+One "step" = the whole hot path on one batch of synthetic input: reset the grid (Init), build the
+2D SDF of every view, fuse all views, extract the iso surface.  Prints ONE JSON line (rank 0).
+  value      Nvox * V / step time, inputs (masks) already resident in HBM, CUDA-event timed
+  e2e        same step through the public host API (VoxelCarver.Carve on pinned HOST masks, mesh
+             copied back to the host), host<->device copies inside the timed region
+  roofline   fusion kernel: algorithmic bytes per launch / measured launch time vs measured HBM peak
+  cpu_baseline   the unmodified reference (oracle/_ref) timed on this box's host cores on a bounded
+             sample of the same workload (N=1 only)
+`--impl reference` times only the reference on the host cores (rank 0; other ranks exit).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from vacancy_b200 import synthetic as S  # noqa: E402
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", p
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)", {}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0]))
+                mx.append(float(p[1]))
+                pw.append(float(p[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)),
+                "power_w_max": float(max(pw)), "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def workload(name):
+    cfg = dict(S.CONFIGS[name])
+    cfg["name"] = name
+    return cfg
+
+
+def describe(cfg):
+    return ("%s: %d^3 grid, %d views %dx%d, %s, marching cubes" %
+            (cfg["name"], cfg["grid"], cfg["views"], cfg["image"], cfg["image"],
+             "weighted-average TSDF (truncation 0.1, max_update_num 255)" if cfg["weighted"]
+             else "kMax update, no truncation"))
+
+
+# ---------------------------------------------------------------------------------------------------
+def reference_sample(cfg, n_views, planes):
+    """Times the UNMODIFIED reference (oracle/_ref) on a bounded sample of the workload: a slab of
+    `planes` z planes of the grid (same voxel size, same bbox in x and y) and `n_views` of its
+    views, each stage timed separately (MakeSignedDistanceField, Carve(camera, sdf),
+    ExtractIsoSurface) like SURVEY.md section 8(d); extrapolated per unit to the whole workload."""
+    from oracle import bindings as B
+    ref = B.RefLib()
+    n, V, size = cfg["grid"], cfg["views"], cfg["image"]
+    planes = min(planes, n)
+    half = planes / n
+    res = float(np.float32(2.0) / np.float32(n))
+    opt = B.make_options((-1.0, -1.0, -half), (1.0, 1.0, half), res, update=int(cfg["weighted"]),
+                         truncation=cfg["weighted"], band=0.1)
+    t0 = time.perf_counter()
+    car = ref.carver(opt)
+    t_init = time.perf_counter() - t0
+    assert car.dims == (n, n, planes), car.dims
+    cams = S.circle_cameras(V, size)
+    pick = [int(round(i * V / n_views)) % V for i in range(n_views)]
+    t_sdf = t_fuse = 0.0
+    for vi in pick:
+        mask = S.silhouette(cams[vi])
+        t_sdf += ref.time_make_sdf(mask, True, cfg["weighted"], 0.1, 1)
+        sdf = ref.make_sdf(mask, None, True, cfg["weighted"], 0.1)
+        oc = B.Camera(size, size, cams[vi].c2w(), *cams[vi]._intrinsics())
+        t_fuse += car.carve_sdf(oc, sdf)
+    tm = []
+    v, f = car.extract_iso(0.0, True, timing=tm)
+    t_mc = tm[0]
+    car.close()
+    scale = n / planes
+    t_full = V * (t_sdf / n_views + t_fuse / n_views * scale) + t_mc * scale
+    nvox = float(n) ** 3
+    return dict(
+        value=nvox * V / t_full / 1e9, t_sample=t_sdf + t_fuse + t_mc, cores=ref.threads(),
+        sample=("%d of %d views on a %dx%dx%d z-slab of the %d^3 grid; per-view SDF %.3f s (1 thread), "
+                "fusion %.3f s/view on the slab (%d OpenMP threads), marching cubes %.3f s on the slab "
+                "(1 thread); extrapolated per unit to the full workload (%.0f s); grid Init %.1f s not "
+                "counted" % (n_views, V, n, n, planes, n, t_sdf / n_views, t_fuse / n_views,
+                             ref.threads(), t_mc, t_full, t_init)),
+        stages=dict(sdf2d_s_per_view=t_sdf / n_views, fusion_s_per_view_slab=t_fuse / n_views,
+                    mc_s_slab=t_mc, fusion_gvv_per_s=nvox / scale * n_views / t_fuse / 1e9,
+                    mc_gvoxel_per_s=nvox / scale / t_mc / 1e9, mesh=[len(v), len(f)]))
+
+
+def run_reference_arm(args, cfg):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    total = args.steps + args.warmup
+    n_views = max(2, min(8, int(48 / max(total, 1))))
+    planes = 32
+    vals, times = [], []
+    last = None
+    for i in range(total):
+        r = reference_sample(cfg, n_views, planes)
+        if i >= args.warmup:
+            vals.append(r["value"])
+            times.append(r["t_sample"])
+            last = r
+    value = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": "carve_gvoxel_view_updates_per_s", "value": value,
+        "unit": "Gvoxel-view/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": float(np.mean(times)) * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": describe(cfg), "host": "CPU only (reference has no GPU path)"},
+        "cpu_baseline": {"value": value, "unit": "Gvoxel-view/s", "cores": last["cores"],
+                         "kind": "reference", "sample": last["sample"], "stages": last["stages"]},
+        "e2e": {"value": value, "unit": "Gvoxel-view/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------
+def run_ours(args, cfg):
+    import torch
+    import torch.distributed as dist
+
+    from vacancy_b200 import sharded
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - this library has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n, V, size = cfg["grid"], cfg["views"], cfg["image"]
+    hbm_peak, peak_src, _ = load_peaks()
+
+    stream = torch.cuda.Stream()
+    car = sharded.ShardedCarver(S.grid_option(n, weighted=cfg["weighted"]), rank, world, local,
+                                stream=stream)
+    cams = S.circle_cameras(V, size)
+    # the sphere at the origin looks the same from every camera on the circle: rasterise once
+    mask0 = S.silhouette(cams[0])
+    host_masks = torch.empty((V, size, size), dtype=torch.uint8, pin_memory=True)
+    host_masks[:] = torch.from_numpy(mask0)
+    dev_masks = host_masks.to("cuda", non_blocking=False)
+    views = car.make_views(cams, size, size)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        car.reset()
+        car.carve_device_masks(views, dev_masks)
+        return car.extract_iso_counts(0.0, True)
+
+    host_np = [host_masks[i].numpy() for i in range(V)]
+
+    def step_e2e():
+        car.reset()
+        car.carve_host_masks(cams, host_np)
+        v, f = car.extract_iso_host(0.0, True)
+        return len(v), len(f), v.nbytes + f.nbytes
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        out = None
+        for _ in range(steps):
+            out = fn()
+        e1.record(stream)
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), out
+
+    for _ in range(args.warmup):
+        step_resident()
+    car.stage_times()  # clear the per-stage counters
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_total, counts = timed(step_resident, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    stages = car.stage_times()
+    ms_step = ms_total / args.steps
+
+    for _ in range(min(args.warmup, 2)):
+        step_e2e()
+    e2e_steps = max(1, min(args.steps, 3))
+    ms_e2e_total, e2e_out = timed(step_e2e, e2e_steps)
+    ms_e2e = ms_e2e_total / e2e_steps
+
+    nvox = float(n) ** 3
+    updates = nvox * V
+    # fusion roofline: algorithmic bytes of one launch = 16 B per owned voxel + 4 B per SDF pixel of
+    # the views in that launch; duration from CUDA events around each launch
+    fus_ms, fus_launches = stages["fusion"]
+    fus_launches -= args.steps  # the grid reset is booked on the same counter
+    views_per_launch = V / max(fus_launches / args.steps, 1)
+    bytes_per_launch = 16.0 * car.slab_voxels + 4.0 * size * size * views_per_launch
+    fus_ms_per_launch = fus_ms / max(fus_launches, 1)
+    achieved = bytes_per_launch / (fus_ms_per_launch * 1e-3) / 1e9
+    launches_per_step = sum(v[1] for v in stages.values()) / args.steps
+
+    line = {
+        "metric": "carve_gvoxel_view_updates_per_s", "value": updates / (ms_step * 1e-3) / 1e9,
+        "unit": "Gvoxel-view/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": describe(cfg), "grid": [n, n, n], "views": V, "image": [size, size],
+                   "parallelism": "z-slab x%d" % world,
+                   "l2": "inputs larger than L2 (masks %.2f GB, grid state %.2f GB per step)"
+                         % (V * size * size / 1e9, 8 * nvox / 1e9),
+                   "step": "reset + 2D SDF of every view + fusion (64 views/launch) + marching cubes"},
+        "clocks": clocks,
+        "e2e": {"value": updates / (ms_e2e * 1e-3) / 1e9, "unit": "Gvoxel-view/s",
+                "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(V * size * size),
+                "d2h_bytes_per_step": int(e2e_out[2]), "steps": e2e_steps,
+                "api": "VoxelCarver.carve_batch(host pinned masks) + ExtractIsoSurface -> host mesh"},
+        "gpu_launches": int(round(launches_per_step * args.steps)),
+        "roofline": {"kernel": "fuse_kernel", "bound": "hbm", "achieved": achieved,
+                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                     "traffic": None, "peak_source": peak_src,
+                     "bytes_per_launch": bytes_per_launch, "ms_per_launch": fus_ms_per_launch,
+                     "note": "batched fusion is FP32/ALU-issue bound, not HBM bound (SURVEY.md 8d); "
+                             "see fp32"},
+        "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items()},
+        "mc": {"ms": stages["marching_cubes"][0] / args.steps,
+               "gvoxel_per_s": nvox / world / (stages["marching_cubes"][0] / args.steps * 1e-3) / 1e9,
+               "vertices": int(counts[0]), "faces": int(counts[1])},
+        "fusion_gvv_per_s": updates / world / (fus_ms / args.steps * 1e-3) / 1e9,
+    }
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    ops = 54.0 if cfg["weighted"] else 48.0  # reference-order FP32 ops per voxel-view, SURVEY.md 8d
+    peak_ops = 148 * 128 * sm_mhz * 1e6
+    line["fp32"] = {"ops_per_voxel_view": ops, "achieved_tops": updates / world * ops /
+                    (fus_ms / args.steps * 1e-3) / 1e12, "peak_tops": peak_ops / 1e12,
+                    "frac": updates / world * ops / (fus_ms / args.steps * 1e-3) / peak_ops,
+                    "note": "upper bound on useful work: voxel-views skipped by the reference's own "
+                            "early-outs are counted as full"}
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            r = reference_sample(cfg, 4, 32)
+            line["cpu_baseline"] = {"value": r["value"], "unit": "Gvoxel-view/s", "cores": r["cores"],
+                                    "kind": "reference", "sample": r["sample"],
+                                    "stages": r["stages"]}
+        except Exception as e:  # the checker being absent must not hide the GPU numbers
+            line["cpu_baseline"] = {"value": None, "unit": "Gvoxel-view/s", "cores": 0,
+                                    "kind": "reference", "sample": "unavailable: %r" % (e,)}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg4", choices=sorted(S.CONFIGS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    cfg = workload(args.workload)
+    if args.impl == "reference":
+        run_reference_arm(args, cfg)
+    else:
+        run_ours(args, cfg)
+
+
+if __name__ == "__main__":
+    main()

@@ -93,6 +93,9 @@ void vcb_options_default(vcb_options* opt);
  * empty bounding box) with VCB_ERR_INVALID.  Unlike the reference, grids above 2^31 voxels are
  * accepted (64-bit indices); a single carver's slab must still hold < 2^31 * 32 voxels. */
 int vcb_create(const vcb_options* opt, vcb_carver** out);
+/* Init() called again on a live carver (voxel_carver.cc:390-391 re-creates the grid): every voxel
+ * back to sdf = kVal, update_num = 0, queued views dropped; buffers are kept. Stream-ordered. */
+int vcb_reset(vcb_carver* c);
 /* VoxelCarver::~VoxelCarver, voxel_carver.cc:369 */
 void vcb_destroy(vcb_carver* c);
 
@@ -150,6 +153,28 @@ int vcb_extract_iso_fill(vcb_carver* c, float* vertices, int32_t* faces);
 /* DEVICE pointers to the mesh left by the last vcb_extract_iso_count (owned by the carver, valid
  * until its next extract call or destroy). */
 int vcb_extract_iso_device(vcb_carver* c, const float** vertices_dev, const int32_t** faces_dev);
+
+/* The same extraction in phases, for a grid sharded into z slabs across GPUs (no reference
+ * counterpart: the reference is single-process; numbering still follows marching_cubes.cc:199-218
+ * over the WHOLE grid).  Per slab, in this order:
+ *   1. fill the halo: the 2 sdf planes below the slab (vcb_halo_device) with the lower slab's top
+ *      planes (vcb_grid_device + offset);                                 [neighbour exchange]
+ *   2. _begin: classify + count -> this slab's vertex / face counts;
+ *   3. all slabs exchange counts; vertex_offset = sum of the lower slabs' vertex counts;
+ *   4. _vertices(vertex_offset): emits this slab's vertices, ids become global;
+ *   5. _export_top(ids): ids (or -1) of the vertices on the x- and y-edges of the slab's top plane,
+ *      2*ny*nx int32 (DEVICE), sent to the slab above, which calls _import_bottom(ids);
+ *   6. _faces: emits this slab's faces with global vertex ids.
+ * vcb_extract_iso_count == _begin + _vertices(0) + _faces. */
+int vcb_extract_iso_begin(vcb_carver* c, double iso_level, int32_t linear_interp,
+                          int64_t* n_vertices, int64_t* n_faces);
+int vcb_extract_iso_vertices(vcb_carver* c, int64_t vertex_offset);
+int vcb_extract_iso_export_top(vcb_carver* c, int32_t* ids_dev);
+int vcb_extract_iso_import_bottom(vcb_carver* c, const int32_t* ids_dev);
+int vcb_extract_iso_faces(vcb_carver* c);
+/* DEVICE pointer to the halo: n_planes (0..2) sdf planes stored directly below the slab
+ * (planes z_begin - n_planes .. z_begin - 1), contiguous with the slab's own planes. */
+int vcb_halo_device(vcb_carver* c, float** halo_dev, int32_t* n_planes);
 
 /* ExtractVoxel(mesh, inside_empty), voxel_carver.cc:530-538 -> extract_voxel.cc:258-317.
  * _count classifies the voxels and returns how many cubes will be emitted (24 vertices and 12

@@ -87,7 +87,7 @@ def random_mask(rng, h, w, kind):
         m = np.zeros((h, w), bool)
         for _ in range(rng.integers(1, 5)):
             cy, cx = rng.uniform(0, h), rng.uniform(0, w)
-            ry, rx = rng.uniform(2, h / 2), rng.uniform(2, w / 2)
+            ry, rx = rng.uniform(1, max(2.0, h / 2)), rng.uniform(1, max(2.0, w / 2))
             m |= ((yy - cy) / ry) ** 2 + ((xx - cx) / rx) ** 2 < 1.0
         return (m * 255).astype(np.uint8)
     if kind == "noise":

@@ -1,0 +1,54 @@
+"""CPU-only tests of the multi-GPU host logic: slab partition, global numbering offsets, and the
+count exchange over a real 2-rank process group (gloo)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from vacancy_b200 import sharded
+
+
+def test_slab_ranges_cover_grid():
+    for nz, world in ((1024, 8), (42, 4), (7, 3), (2048, 8), (5, 2)):
+        r = sharded.slab_ranges(nz, world)
+        assert r[0][0] == 0 and r[-1][1] == nz and len(r) == world
+        assert all(a[1] == b[0] for a, b in zip(r[:-1], r[1:]))
+        sizes = [b - a for a, b in r]
+        assert min(sizes) >= 2 and max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        sharded.slab_ranges(7, 4)
+
+
+def test_exclusive_offsets():
+    off, total = sharded.exclusive_offsets([(5, 9), (0, 0), (7, 2)])
+    assert off.tolist() == [[0, 0], [5, 9], [5, 9]] and total.tolist() == [12, 11]
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    off, total = sharded.gather_offsets(100 * (rank + 1), 7 + rank, world)
+    q.put((rank, off.tolist(), total.tolist()))
+    dist.destroy_process_group()
+
+
+def test_count_exchange_world2_gloo():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, off, total in res:
+        assert off == [[0, 0], [100, 7]] and total == [300, 15]

@@ -34,11 +34,13 @@ class View(C.Structure):
 
 
 EXPORTS = [
-    "vcb_last_error", "vcb_invalid_sdf", "vcb_options_default", "vcb_create", "vcb_destroy",
+    "vcb_last_error", "vcb_invalid_sdf", "vcb_options_default", "vcb_create", "vcb_reset", "vcb_destroy",
     "vcb_grid_dims", "vcb_slab_range", "vcb_grid_positions", "vcb_set_stream", "vcb_synchronize",
     "vcb_flush", "vcb_carve_masks", "vcb_carve_masks_device", "vcb_carve_sdfs",
     "vcb_carve_sdfs_device", "vcb_distance_transform_l1", "vcb_make_signed_distance_field",
     "vcb_extract_iso_count", "vcb_extract_iso_fill", "vcb_extract_iso_device",
+    "vcb_extract_iso_begin", "vcb_extract_iso_vertices", "vcb_extract_iso_export_top",
+    "vcb_extract_iso_import_bottom", "vcb_extract_iso_faces", "vcb_halo_device",
     "vcb_extract_voxel_count", "vcb_extract_voxel_fill", "vcb_extract_voxel_occupancy",
     "vcb_download_grid", "vcb_upload_grid", "vcb_grid_device", "vcb_stage_times",
 ]
@@ -64,6 +66,7 @@ def load_library(path=LIB_PATH):
     L.vcb_options_default.argtypes = [C.POINTER(Options)]
     L.vcb_options_default.restype = None
     L.vcb_create.argtypes = [C.POINTER(Options), C.POINTER(vp)]
+    L.vcb_reset.argtypes = [vp]
     L.vcb_destroy.argtypes = [vp]
     L.vcb_destroy.restype = None
     L.vcb_grid_dims.argtypes = [vp, ip]
@@ -81,6 +84,12 @@ def load_library(path=LIB_PATH):
     L.vcb_make_signed_distance_field.argtypes = [i32, u8p, i32, i32, ip, ip, i32, i32, C.c_float,
                                                  fp]
     L.vcb_extract_iso_count.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
+    L.vcb_extract_iso_begin.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
+    L.vcb_extract_iso_vertices.argtypes = [vp, i64]
+    L.vcb_extract_iso_export_top.argtypes = [vp, vp]
+    L.vcb_extract_iso_import_bottom.argtypes = [vp, vp]
+    L.vcb_extract_iso_faces.argtypes = [vp]
+    L.vcb_halo_device.argtypes = [vp, C.POINTER(vp), ip]
     L.vcb_extract_iso_fill.argtypes = [vp, fp, ip]
     L.vcb_extract_iso_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     L.vcb_extract_voxel_count.argtypes = [vp, i32, C.POINTER(i64)]

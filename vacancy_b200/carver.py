@@ -342,6 +342,10 @@ class VoxelCarver:
             self._h, *(a.ctypes.data_as(C.POINTER(C.c_float)) for a in (px, py, pz))))
         return px, py, pz
 
+    def reset(self):
+        """Init() again on the same carver: grid back to its initial state, buffers kept."""
+        self._check(self._lib.vcb_reset(self._h))
+
     def set_stream(self, cuda_stream):
         self._check(self._lib.vcb_set_stream(self._h, C.c_void_p(cuda_stream)))
 

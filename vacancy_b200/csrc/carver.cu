@@ -24,6 +24,21 @@ namespace {
 
 thread_local std::string g_last_error = "";
 
+// VoxelGrid::Init's state: sdf = kVal, update_num = 0 (voxel_carver.cc:342, voxel_carver.h:67-68)
+__global__ void __launch_bounds__(256) grid_reset_kernel(float4* __restrict__ sdf4,
+                                                         int4* __restrict__ un4, size_t n4_sdf,
+                                                         size_t n4_un, float* __restrict__ sdf_tail,
+                                                         int* __restrict__ un_tail, int tail_sdf,
+                                                         int tail_un) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const float4 k4 = make_float4(kInvalidSdf, kInvalidSdf, kInvalidSdf, kInvalidSdf);
+  for (size_t i = t; i < n4_sdf; i += stride) sdf4[i] = k4;
+  for (size_t i = t; i < n4_un; i += stride) un4[i] = make_int4(0, 0, 0, 0);
+  if (t < (size_t)tail_sdf) sdf_tail[t] = kInvalidSdf;
+  if (t < (size_t)tail_un) un_tail[t] = 0;
+}
+
 struct TimedSpan {
   cudaEvent_t a, b;
   int stage;
@@ -210,6 +225,16 @@ GridDesc grid_desc(const vcb_carver* c) {
 
 int64_t slab_voxels(const vcb_carver* c) {
   return (int64_t)c->nx * c->ny * (c->z_end - c->z_begin);
+}
+
+void launch_grid_reset(vcb_carver* c) {
+  const size_t plane = (size_t)c->nx * c->ny;
+  const size_t n_sdf = plane * (size_t)(c->z_end - c->z_begin + c->halo);
+  const size_t n_un = plane * (size_t)(c->z_end - c->z_begin);
+  // cudaMalloc pointers are 256-byte aligned, so the float4 / int4 views start aligned
+  grid_reset_kernel<<<148 * 8, 256, 0, c->stream>>>(
+      reinterpret_cast<float4*>(c->sdf_alloc), reinterpret_cast<int4*>(c->un), n_sdf / 4, n_un / 4,
+      c->sdf_alloc + (n_sdf / 4) * 4, c->un + (n_un / 4) * 4, (int)(n_sdf % 4), (int)(n_un % 4));
 }
 
 // launches the fusion kernel over the queued views
@@ -423,15 +448,9 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
   }
   CREATE_TRY(c->max_sdf.reserve(sizeof(float) * kMaxViewsPerLaunch));
   // sdf = kVal, update_num = 0 (voxel_carver.cc:342, voxel_carver.h:67-68)
-  {
-    // -FLT_MAX is 0xFF7FFFFF: not a byte pattern, so fill through a tiny kernel-free path:
-    std::vector<float> row(plane, kInvalidSdf);
-    for (int z = 0; z < (z1 - z0) + c->halo; z++) {
-      CREATE_TRY(cudaMemcpy(c->sdf_alloc + (size_t)z * plane, row.data(), plane * sizeof(float),
-                            cudaMemcpyHostToDevice));
-    }
-    CREATE_TRY(cudaMemset(c->un, 0, n * sizeof(int32_t)));
-  }
+  launch_grid_reset(c);
+  CREATE_TRY(cudaGetLastError());
+  CREATE_TRY(cudaStreamSynchronize(c->stream));
   memset(&c->fp, 0, sizeof(c->fp));
   c->fp.sdf = c->sdf;
   c->fp.update_num = c->un;
@@ -471,6 +490,20 @@ void vcb_destroy(vcb_carver* c) {
                     &c->iso.verts, &c->iso.faces, &c->iso.counters};
   for (Scratch* s : all) s->release();
   delete c;
+}
+
+int vcb_reset(vcb_carver* c) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  c->pending = 0;  // views queued but not yet fused belong to the grid being discarded
+  launch_grid_reset(c);
+  c->stage_launches[1] += 1;
+  c->un_implied = true;
+  c->iso.n_vertices = c->iso.n_faces = -1;
+  c->vox.n_voxels = -1;
+  CU(c, cudaGetLastError());
+  return VCB_OK;
 }
 
 int vcb_grid_dims(const vcb_carver* c, int32_t dims3[3]) {
@@ -660,15 +693,15 @@ int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t 
                            minmax_normalize, use_truncation, truncation_band, dist);
 }
 
-int vcb_extract_iso_count(vcb_carver* c, double iso_level, int32_t linear_interp,
+int vcb_extract_iso_begin(vcb_carver* c, double iso_level, int32_t linear_interp,
                           int64_t* n_vertices, int64_t* n_faces) {
   if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
   int rc = vcb_flush(c);
   if (rc != VCB_OK) return rc;
   {
     Span span(c, 3);
-    cudaError_t e = iso_extract(grid_desc(c), c->un_implied, iso_level, linear_interp, &c->iso,
-                                c->stream, &c->stage_launches[3]);
+    cudaError_t e = iso_count(grid_desc(c), c->un_implied, iso_level, linear_interp, &c->iso,
+                              c->stream, &c->stage_launches[3]);
     if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "marching cubes: %s", cudaGetErrorString(e));
   }
   if (c->iso.n_vertices > INT32_MAX || c->iso.n_faces > INT32_MAX)
@@ -678,9 +711,74 @@ int vcb_extract_iso_count(vcb_carver* c, double iso_level, int32_t linear_interp
   return VCB_OK;
 }
 
+int vcb_extract_iso_vertices(vcb_carver* c, int64_t vertex_offset) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (c->iso.phase != 1) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_begin has not run");
+  if (vertex_offset < 0 || vertex_offset + c->iso.n_vertices > INT32_MAX)
+    return fail(c, VCB_ERR_UNSUPPORTED, "vertex ids exceed int32 (mesh.cc:241-271)");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  Span span(c, 3);
+  cudaError_t e = iso_emit_vertices(grid_desc(c), vertex_offset, &c->iso, c->stream,
+                                    &c->stage_launches[3]);
+  if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "marching cubes vertices: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
+int vcb_extract_iso_export_top(vcb_carver* c, int32_t* ids_dev) {
+  if (!c || !ids_dev) return fail(c, VCB_ERR_INVALID, "null argument");
+  if (c->iso.phase < 2) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_vertices has not run");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  Span span(c, 3);
+  cudaError_t e = iso_export_top_ids(grid_desc(c), &c->iso, ids_dev, c->stream,
+                                     &c->stage_launches[3]);
+  if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "export ids: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
+int vcb_extract_iso_import_bottom(vcb_carver* c, const int32_t* ids_dev) {
+  if (!c || !ids_dev) return fail(c, VCB_ERR_INVALID, "null argument");
+  if (c->iso.phase != 2) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_vertices has not run");
+  if (c->z_begin < 1) return fail(c, VCB_ERR_INVALID, "the first slab has no slab below it");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  Span span(c, 3);
+  cudaError_t e = iso_import_bottom_ids(grid_desc(c), &c->iso, ids_dev, c->stream,
+                                        &c->stage_launches[3]);
+  if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "import ids: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
+int vcb_extract_iso_faces(vcb_carver* c) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (c->iso.phase != 2) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_vertices has not run");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  Span span(c, 3);
+  cudaError_t e = iso_emit_faces(grid_desc(c), &c->iso, c->stream, &c->stage_launches[3]);
+  if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "marching cubes faces: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
+int vcb_extract_iso_count(vcb_carver* c, double iso_level, int32_t linear_interp,
+                          int64_t* n_vertices, int64_t* n_faces) {
+  int rc = vcb_extract_iso_begin(c, iso_level, linear_interp, n_vertices, n_faces);
+  if (rc != VCB_OK) return rc;
+  if ((rc = vcb_extract_iso_vertices(c, 0)) != VCB_OK) return rc;
+  return vcb_extract_iso_faces(c);
+}
+
+int vcb_halo_device(vcb_carver* c, float** halo_dev, int32_t* n_planes) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (halo_dev) *halo_dev = c->sdf_alloc;
+  if (n_planes) *n_planes = c->halo;
+  return VCB_OK;
+}
+
 int vcb_extract_iso_fill(vcb_carver* c, float* vertices, int32_t* faces) {
   if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
-  if (c->iso.n_vertices < 0) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_count has not run");
+  if (c->iso.phase != 3) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_count has not run");
   int rc = use_device(c, c->opt.device);
   if (rc != VCB_OK) return rc;
   if (vertices && c->iso.n_vertices > 0)
@@ -695,7 +793,7 @@ int vcb_extract_iso_fill(vcb_carver* c, float* vertices, int32_t* faces) {
 
 int vcb_extract_iso_device(vcb_carver* c, const float** vertices_dev, const int32_t** faces_dev) {
   if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
-  if (c->iso.n_vertices < 0) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_count has not run");
+  if (c->iso.phase != 3) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_count has not run");
   if (vertices_dev) *vertices_dev = static_cast<const float*>(c->iso.verts.ptr);
   if (faces_dev) *faces_dev = static_cast<const int32_t*>(c->iso.faces.ptr);
   return VCB_OK;

@@ -112,9 +112,22 @@ struct IsoExtract {
   Scratch ibits, vbits, cbits, abits, segcnt, segbase, active, tmp, hkeys, hvals, verts, faces,
       counters;
   int64_t n_vertices = -1, n_faces = -1;
+  int phase = 0;          // 0 nothing, 1 counted, 2 vertices emitted, 3 faces emitted
+  unsigned n_active = 0;  // active segments
+  uint64_t hmask = 0;
+  double iso_level = 0.0;
+  int linear_interp = 1;
 };
-cudaError_t iso_extract(const GridDesc& g, bool un_implied, double iso_level, int linear_interp,
-                        IsoExtract* st, cudaStream_t stream, int64_t* launches);
+cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int linear_interp,
+                      IsoExtract* st, cudaStream_t stream, int64_t* launches);
+cudaError_t iso_emit_vertices(const GridDesc& g, int64_t vertex_offset, IsoExtract* st,
+                              cudaStream_t stream, int64_t* launches);
+cudaError_t iso_export_top_ids(const GridDesc& g, IsoExtract* st, int32_t* out_dev,
+                               cudaStream_t stream, int64_t* launches);
+cudaError_t iso_import_bottom_ids(const GridDesc& g, IsoExtract* st, const int32_t* in_dev,
+                                  cudaStream_t stream, int64_t* launches);
+cudaError_t iso_emit_faces(const GridDesc& g, IsoExtract* st, cudaStream_t stream,
+                           int64_t* launches);
 
 void init_mc_tables();  // uploads the constant-memory tables once per device
 

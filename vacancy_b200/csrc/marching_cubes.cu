@@ -445,14 +445,50 @@ static float iso_threshold(double iso) {
   return t;
 }
 
-cudaError_t iso_extract(const GridDesc& g, bool un_implied, double iso_level, int linear_interp,
-                        IsoExtract* st, cudaStream_t stream, int64_t* launches) {
-  const McGeom m = mc_geom(g);
-  st->n_vertices = st->n_faces = -1;
-  if (m.n_segs >= (int64_t)0xffffffffll) return cudaErrorInvalidValue;
-  cudaError_t e;
+namespace {
+
+// x- and y-edges lying in one voxel plane: id of the vertex on each (or -1). Used to hand the
+// vertices on a slab's top plane to the slab above it.
+__global__ void __launch_bounds__(256)
+    mc_export_plane_kernel(int nx, int ny, int z, const uint64_t* __restrict__ hkeys,
+                           const int32_t* __restrict__ hvals, uint64_t hmask,
+                           int32_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t n = (int64_t)nx * ny;
+  if (i >= 2 * n) return;
+  const int axis = (int)(i / n);
+  const uint64_t id = (uint64_t)z * n + (uint64_t)(i % n);  // lower endpoint of the edge
+  out[i] = hkeys ? hash_find(hkeys, hvals, hmask, (id << 2) | (uint64_t)axis) : -1;
+}
+
+__global__ void __launch_bounds__(256)
+    mc_import_plane_kernel(int nx, int ny, int z, const int32_t* __restrict__ in, uint64_t* hkeys,
+                           int32_t* hvals, uint64_t hmask) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t n = (int64_t)nx * ny;
+  if (i >= 2 * n) return;
+  const int32_t v = in[i];
+  if (v < 0) return;
+  const int axis = (int)(i / n);
+  const uint64_t id = (uint64_t)z * n + (uint64_t)(i % n);
+  hash_insert(hkeys, hvals, hmask, (id << 2) | (uint64_t)axis, v);
+}
+
+}  // namespace
+
 #define VCB_TRY(x) \
   if ((e = (x)) != cudaSuccess) return e
+
+// Phase 1: classification, counts and the raster-order prefix sums. Leaves n_vertices / n_faces.
+cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int linear_interp,
+                      IsoExtract* st, cudaStream_t stream, int64_t* launches) {
+  const McGeom m = mc_geom(g);
+  st->n_vertices = st->n_faces = -1;
+  st->phase = 0;
+  st->iso_level = iso_level;
+  st->linear_interp = linear_interp;
+  if (m.n_segs >= (int64_t)0xffffffffll) return cudaErrorInvalidValue;
+  cudaError_t e;
   const size_t wbytes = (size_t)m.n_words * sizeof(uint32_t);
   VCB_TRY(st->ibits.reserve(wbytes));
   VCB_TRY(st->vbits.reserve(wbytes));
@@ -492,6 +528,7 @@ cudaError_t iso_extract(const GridDesc& g, bool un_implied, double iso_level, in
   unsigned h_active = 0;
   VCB_TRY(cudaMemcpyAsync(&h_active, n_active, sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
   VCB_TRY(cudaStreamSynchronize(stream));
+  st->n_active = h_active;
   const unsigned wblocks = (h_active + 3) / 4;  // 4 warps per block
   if (h_active > 0) {
     mc_count_kernel<<<wblocks, 128, 0, stream>>>(m, ibits, cbits, abits, active, n_active, segcnt);
@@ -504,30 +541,82 @@ cudaError_t iso_extract(const GridDesc& g, bool un_implied, double iso_level, in
   VCB_TRY(cudaMemcpyAsync(&total, segbase + m.n_segs, sizeof(total), cudaMemcpyDeviceToHost,
                           stream));
   VCB_TRY(cudaStreamSynchronize(stream));
-  const int64_t nv = (int64_t)(total >> 32), nf = (int64_t)(total & 0xffffffffull);
-  if (nv > 0) {
-    uint64_t cap = 1024;
-    while (cap < (uint64_t)nv * 2) cap <<= 1;
-    VCB_TRY(st->hkeys.reserve(cap * sizeof(uint64_t)));
-    VCB_TRY(st->hvals.reserve(cap * sizeof(int32_t)));
-    VCB_TRY(st->verts.reserve((size_t)nv * 3 * sizeof(float)));
-    VCB_TRY(st->faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int32_t)));
-    VCB_TRY(cudaMemsetAsync(st->hkeys.ptr, 0xff, cap * sizeof(uint64_t), stream));
-    mc_vertex_kernel<<<wblocks, 128, 0, stream>>>(
-        m, g, ibits, cbits, abits, active, n_active, segbase, iso_level, linear_interp, 0,
-        static_cast<float*>(st->verts.ptr), static_cast<uint64_t*>(st->hkeys.ptr),
-        static_cast<int32_t*>(st->hvals.ptr), cap - 1);
-    mc_face_kernel<<<wblocks, 128, 0, stream>>>(
-        m, ibits, abits, active, n_active, segbase, static_cast<int32_t*>(st->faces.ptr),
-        static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), cap - 1);
-    if (launches) *launches += 2;
-  }
-#undef VCB_TRY
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  st->n_vertices = nv;
-  st->n_faces = nf;
+  st->n_vertices = (int64_t)(total >> 32);
+  st->n_faces = (int64_t)(total & 0xffffffffull);
+  st->phase = 1;
   return cudaSuccess;
 }
+
+// Phase 2: vertices at their final local index; ids stored in the edge hash are global
+// (local index + vertex_offset).
+cudaError_t iso_emit_vertices(const GridDesc& g, int64_t vertex_offset, IsoExtract* st,
+                              cudaStream_t stream, int64_t* launches) {
+  if (st->phase != 1) return cudaErrorInvalidValue;
+  const McGeom m = mc_geom(g);
+  cudaError_t e;
+  const int64_t nv = st->n_vertices, nf = st->n_faces;
+  // slots for the vertices handed over by the slab below (at most one per in-plane edge)
+  const uint64_t imported = g.z_begin > 0 ? 2ull * g.nx * g.ny : 0ull;
+  uint64_t cap = 1024;
+  while (cap < ((uint64_t)nv + imported) * 2) cap <<= 1;
+  st->hmask = cap - 1;
+  VCB_TRY(st->hkeys.reserve(cap * sizeof(uint64_t)));
+  VCB_TRY(st->hvals.reserve(cap * sizeof(int32_t)));
+  VCB_TRY(st->verts.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float)));
+  VCB_TRY(st->faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int32_t)));
+  VCB_TRY(cudaMemsetAsync(st->hkeys.ptr, 0xff, cap * sizeof(uint64_t), stream));
+  if (st->n_active > 0 && nv > 0) {
+    mc_vertex_kernel<<<(st->n_active + 3) / 4, 128, 0, stream>>>(
+        m, g, static_cast<uint32_t*>(st->ibits.ptr), static_cast<uint32_t*>(st->cbits.ptr),
+        static_cast<uint32_t*>(st->abits.ptr), static_cast<uint32_t*>(st->active.ptr),
+        static_cast<unsigned*>(st->counters.ptr), static_cast<uint64_t*>(st->segbase.ptr),
+        st->iso_level, st->linear_interp, vertex_offset, static_cast<float*>(st->verts.ptr),
+        static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), st->hmask);
+    if (launches) *launches += 1;
+  }
+  st->phase = 2;
+  return cudaGetLastError();
+}
+
+cudaError_t iso_export_top_ids(const GridDesc& g, IsoExtract* st, int32_t* out_dev,
+                               cudaStream_t stream, int64_t* launches) {
+  if (st->phase < 2) return cudaErrorInvalidValue;
+  const int64_t n2 = 2ll * g.nx * g.ny;
+  mc_export_plane_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, stream>>>(
+      g.nx, g.ny, g.z_end - 1, static_cast<uint64_t*>(st->hkeys.ptr),
+      static_cast<int32_t*>(st->hvals.ptr), st->hmask, out_dev);
+  if (launches) *launches += 1;
+  return cudaGetLastError();
+}
+
+cudaError_t iso_import_bottom_ids(const GridDesc& g, IsoExtract* st, const int32_t* in_dev,
+                                  cudaStream_t stream, int64_t* launches) {
+  if (st->phase != 2 || g.z_begin < 1) return cudaErrorInvalidValue;
+  const int64_t n2 = 2ll * g.nx * g.ny;
+  mc_import_plane_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, stream>>>(
+      g.nx, g.ny, g.z_begin - 1, in_dev, static_cast<uint64_t*>(st->hkeys.ptr),
+      static_cast<int32_t*>(st->hvals.ptr), st->hmask);
+  if (launches) *launches += 1;
+  return cudaGetLastError();
+}
+
+// Phase 3: triangles in table order with ids looked up by edge key.
+cudaError_t iso_emit_faces(const GridDesc& g, IsoExtract* st, cudaStream_t stream,
+                           int64_t* launches) {
+  if (st->phase != 2) return cudaErrorInvalidValue;
+  const McGeom m = mc_geom(g);
+  if (st->n_active > 0 && st->n_faces > 0) {
+    mc_face_kernel<<<(st->n_active + 3) / 4, 128, 0, stream>>>(
+        m, static_cast<uint32_t*>(st->ibits.ptr), static_cast<uint32_t*>(st->abits.ptr),
+        static_cast<uint32_t*>(st->active.ptr), static_cast<unsigned*>(st->counters.ptr),
+        static_cast<uint64_t*>(st->segbase.ptr), static_cast<int32_t*>(st->faces.ptr),
+        static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), st->hmask);
+    if (launches) *launches += 1;
+  }
+  st->phase = 3;
+  return cudaGetLastError();
+}
+
+#undef VCB_TRY
 
 }  // namespace vcb
