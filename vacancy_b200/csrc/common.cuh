@@ -29,6 +29,7 @@ struct FuseView {
   int roi_min_xi, roi_min_yi, roi_max_xi, roi_max_yi;
   int pitch;           // image width in pixels
   int model;           // VCB_CAMERA_*
+  int fast;            // set by launch_fusion: pinhole with intrinsics in the shared-reciprocal range
   const float* image;  // device SDF image
   const float* max_sdf;  // device scalar: max over the whole image (only read for VCB_OUTSIDE_MAX)
 };
@@ -69,7 +70,7 @@ void launch_sdf2d(const SdfView* views_dev, const SdfView* views_host, int n_vie
                   int normalize, int truncate, float band, cudaStream_t stream, int64_t* launches);
 void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_t stream,
                       int64_t* launches);
-void launch_fusion(const FuseParams& p, int interp, int update, cudaStream_t stream,
+void launch_fusion(FuseParams& p, int interp, int update, cudaStream_t stream,
                    int64_t* launches);
 
 // ---- extraction ----
