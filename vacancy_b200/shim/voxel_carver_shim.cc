@@ -1,0 +1,335 @@
+// Drop-in replacement for the reference's src/vacancy/voxel_carver.cc, marching_cubes*.cc and
+// extract_voxel.cc: it implements every symbol that include/vacancy/voxel_carver.h declares
+// (voxel_carver.h:39-128), against the reference's UNCHANGED headers, on top of the C ABI of
+// libvacancy_b200.so (include/vacancy_b200.h).  Host code written for the reference - examples.cc
+// for one - compiles and links against it without a source change.
+//
+// What runs where: DistanceTransformL1 / MakeSignedDistanceField, Carve, ExtractVoxel and
+// ExtractIsoSurface run on the GPU through the C ABI, with no CPU fallback - if the library
+// reports an error the call logs it with LOGE and returns false (or leaves the mesh empty), the
+// reference's own error convention.  SignedDistance2Color (a debugging colour
+// map, not on the carving path) and the small VoxelGrid value class stay ordinary host code.
+//
+// The reference class has no member that could hold a device handle (voxel_carver.h:95-97), and the
+// header must not change, so carvers are tracked in a side table keyed by `this`; the AoS
+// `voxel_grid_` member is simply never allocated (the grid lives on the device as SoA).
+#include "vacancy/voxel_carver.h"
+
+#include <cstring>
+#include <limits>
+#include <mutex>
+#include <unordered_map>
+
+#include "vacancy_b200.h"
+
+namespace {
+
+std::mutex g_mutex;
+std::unordered_map<const vacancy::VoxelCarver*, vcb_carver*> g_carvers;
+
+vcb_carver* find_carver(const vacancy::VoxelCarver* self) {
+  std::lock_guard<std::mutex> lock(g_mutex);
+  auto it = g_carvers.find(self);
+  return it == g_carvers.end() ? nullptr : it->second;
+}
+
+void drop_carver(const vacancy::VoxelCarver* self) {
+  vcb_carver* h = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    auto it = g_carvers.find(self);
+    if (it != g_carvers.end()) {
+      h = it->second;
+      g_carvers.erase(it);
+    }
+  }
+  if (h != nullptr) vcb_destroy(h);
+}
+
+int device_ordinal() {
+  const char* e = std::getenv("VACANCY_B200_DEVICE");
+  return e != nullptr ? std::atoi(e) : 0;
+}
+
+// Camera -> vcb_view. The fusion kernel restates exactly two projection models (camera.cc:131-137
+// and :201-205); any other subclass of the abstract Camera cannot run on the device.
+bool make_view(const vacancy::Camera& camera, int width, int height,
+               const Eigen::Vector2i& roi_min, const Eigen::Vector2i& roi_max, vcb_view* v) {
+  std::memset(v, 0, sizeof(*v));
+  const Eigen::Affine3f w2c = camera.w2c().cast<float>();  // voxel_carver.cc:438
+  for (int r = 0; r < 3; r++) {
+    for (int c = 0; c < 4; c++) v->w2c[r * 4 + c] = w2c.matrix()(r, c);
+  }
+  if (const auto* pin = dynamic_cast<const vacancy::PinholeCamera*>(&camera)) {
+    v->model = VCB_CAMERA_PINHOLE;
+    v->fx = pin->focal_length()[0];
+    v->fy = pin->focal_length()[1];
+    v->cx = pin->principal_point()[0];
+    v->cy = pin->principal_point()[1];
+  } else if (dynamic_cast<const vacancy::OrthoCamera*>(&camera) != nullptr) {
+    v->model = VCB_CAMERA_ORTHO;
+  } else {
+    vacancy::LOGE("VoxelCarver::Carve unsupported Camera subclass (pinhole and ortho only)\n");
+    return false;
+  }
+  v->width = width;
+  v->height = height;
+  v->roi_min[0] = roi_min.x();
+  v->roi_min[1] = roi_min.y();
+  v->roi_max[0] = roi_max.x();
+  v->roi_max[1] = roi_max.y();
+  return true;
+}
+
+bool report(const vcb_carver* h, int rc, const char* what) {
+  if (rc == VCB_OK) return true;
+  vacancy::LOGE("%s: %s\n", what, vcb_last_error(h));
+  return false;
+}
+
+}  // namespace
+
+namespace vacancy {
+
+const float InvalidSdf::kVal = std::numeric_limits<float>::lowest();
+
+// ---- free functions, voxel_carver.h:120-128 -----------------------------------------------------
+void DistanceTransformL1(const Image1b& mask, const Eigen::Vector2i& roi_min,
+                         const Eigen::Vector2i& roi_max, Image1f* dist) {
+  dist->Init(mask.width(), mask.height(), 0.0f);
+  const int32_t rmin[2] = {roi_min.x(), roi_min.y()}, rmax[2] = {roi_max.x(), roi_max.y()};
+  report(nullptr,
+         vcb_distance_transform_l1(device_ordinal(), mask.data().data(), mask.width(),
+                                   mask.height(), rmin, rmax, dist->data_ptr()->data()),
+         "DistanceTransformL1");
+}
+
+void MakeSignedDistanceField(const Image1b& mask, const Eigen::Vector2i& roi_min,
+                             const Eigen::Vector2i& roi_max, Image1f* dist,
+                             bool minmax_normalize, bool use_truncation, float truncation_band) {
+  dist->Init(mask.width(), mask.height(), 0.0f);
+  const int32_t rmin[2] = {roi_min.x(), roi_min.y()}, rmax[2] = {roi_max.x(), roi_max.y()};
+  report(nullptr,
+         vcb_make_signed_distance_field(device_ordinal(), mask.data().data(), mask.width(),
+                                        mask.height(), rmin, rmax, minmax_normalize ? 1 : 0,
+                                        use_truncation ? 1 : 0, truncation_band,
+                                        dist->data_ptr()->data()),
+         "MakeSignedDistanceField");
+}
+
+// Debugging colour map (examples.cc:131-133); host code, outside the accelerated path.
+// Positive distances fade from white to red, negative ones from white to blue.
+void SignedDistance2Color(const Image1f& sdf, Image3b* vis_sdf, float min_negative_d,
+                          float max_positive_d) {
+  assert(min_negative_d < 0 && 0 < max_positive_d && vis_sdf != nullptr);
+  vis_sdf->Init(sdf.width(), sdf.height());
+  const float* src = sdf.data().data();
+  uint8_t* dst = vis_sdf->data_ptr()->data();
+  const size_t n = static_cast<size_t>(sdf.width()) * sdf.height();
+  for (size_t i = 0; i < n; i++) {
+    const float d = src[i];
+    const bool positive = d > 0;
+    float t = positive ? (max_positive_d - d) / max_positive_d
+                       : (d - min_negative_d) / (-min_negative_d);
+    t = std::min(std::max(t, 0.0f), 1.0f);
+    const uint8_t faded = static_cast<uint8_t>(255 * t);
+    dst[3 * i + 0] = positive ? 255 : faded;
+    dst[3 * i + 1] = faded;
+    dst[3 * i + 2] = positive ? faded : 255;
+  }
+}
+
+// ---- Voxel / VoxelGrid: plain host value types kept for source compatibility ----------------------
+Voxel::Voxel() {}
+Voxel::~Voxel() {}
+VoxelGrid::VoxelGrid() {}
+VoxelGrid::~VoxelGrid() {}
+
+bool VoxelGrid::Init(const Eigen::Vector3f& bb_max, const Eigen::Vector3f& bb_min,
+                     float resolution) {
+  if (resolution < std::numeric_limits<float>::min()) {
+    LOGE("resolution must be positive %f\n", resolution);
+    return false;
+  }
+  if ((bb_max.array() <= bb_min.array()).any()) {
+    LOGE("input bounding box is invalid\n");
+    return false;
+  }
+  bb_max_ = bb_max;
+  bb_min_ = bb_min;
+  resolution_ = resolution;
+  const Eigen::Vector3f diff = bb_max_ - bb_min_;
+  for (int a = 0; a < 3; a++) voxel_num_[a] = static_cast<int>(diff[a] / resolution_);
+  xy_slice_num_ = voxel_num_[0] * voxel_num_[1];
+  voxels_.assign(static_cast<size_t>(xy_slice_num_) * voxel_num_[2], Voxel());
+  const float half = resolution_ * 0.5f;
+  int id = 0;
+  for (int z = 0; z < voxel_num_[2]; z++) {
+    for (int y = 0; y < voxel_num_[1]; y++) {
+      for (int x = 0; x < voxel_num_[0]; x++, id++) {
+        Voxel& v = voxels_[id];
+        v.index = Eigen::Vector3i(x, y, z);
+        v.id = id;
+        const int k[3] = {x, y, z};
+        for (int a = 0; a < 3; a++) {
+          v.pos[a] = diff[a] * (static_cast<float>(k[a]) / static_cast<float>(voxel_num_[a])) +
+                     bb_min_[a] + half;
+        }
+        v.sdf = InvalidSdf::kVal;
+      }
+    }
+  }
+  return true;
+}
+
+const Eigen::Vector3i& VoxelGrid::voxel_num() const { return voxel_num_; }
+const Voxel& VoxelGrid::get(int x, int y, int z) const {
+  return voxels_[z * xy_slice_num_ + (y * voxel_num_.x() + x)];
+}
+Voxel* VoxelGrid::get_ptr(int x, int y, int z) {
+  return &voxels_[z * xy_slice_num_ + (y * voxel_num_.x() + x)];
+}
+float VoxelGrid::resolution() const { return resolution_; }
+void VoxelGrid::ResetOnSurface() {
+  for (Voxel& v : voxels_) v.on_surface = false;
+}
+bool VoxelGrid::initialized() const { return !voxels_.empty(); }
+
+// ---- VoxelCarver, voxel_carver.h:95-118 ----------------------------------------------------------
+VoxelCarver::VoxelCarver() {}
+VoxelCarver::~VoxelCarver() { drop_carver(this); }
+VoxelCarver::VoxelCarver(VoxelCarverOption option) { set_option(option); }
+void VoxelCarver::set_option(VoxelCarverOption option) { option_ = option; }
+
+bool VoxelCarver::Init() {  // voxel_carver.cc:375-392; calling it again re-creates the grid
+  drop_carver(this);
+  vcb_options o;
+  vcb_options_default(&o);
+  for (int a = 0; a < 3; a++) {
+    o.bb_max[a] = option_.bb_max[a];
+    o.bb_min[a] = option_.bb_min[a];
+  }
+  o.resolution = option_.resolution;
+  o.sdf_minmax_normalize = option_.sdf_minmax_normalize ? 1 : 0;
+  const VoxelUpdateOption& u = option_.update_option;
+  o.voxel_update = static_cast<int32_t>(u.voxel_update);
+  o.sdf_interp = static_cast<int32_t>(u.sdf_interp);
+  o.update_outside = static_cast<int32_t>(u.update_outside);
+  o.voxel_max_update_num = u.voxel_max_update_num;
+  o.voxel_update_weight = u.voxel_update_weight;
+  o.use_truncation = u.use_truncation ? 1 : 0;
+  o.truncation_band = u.truncation_band;
+  o.device = device_ordinal();
+  vcb_carver* h = nullptr;
+  if (!report(nullptr, vcb_create(&o, &h), "VoxelCarver::Init")) return false;
+  std::lock_guard<std::mutex> lock(g_mutex);
+  g_carvers[this] = h;
+  return true;
+}
+
+bool VoxelCarver::Carve(const Camera& camera, const Image1b& silhouette,
+                        const Eigen::Vector2i& roi_min, const Eigen::Vector2i& roi_max,
+                        Image1f* sdf) {
+  vcb_carver* h = find_carver(this);
+  if (h == nullptr) {  // the reference dereferences a null grid here (voxel_carver.cc:397)
+    LOGE("VoxelCarver::Carve voxel grid has not been initialized\n");
+    return false;
+  }
+  vcb_view view;
+  if (!make_view(camera, silhouette.width(), silhouette.height(), roi_min, roi_max, &view)) {
+    return false;
+  }
+  const uint8_t* mask = silhouette.data().data();
+  float* out = nullptr;
+  if (sdf != nullptr) {  // filled like voxel_carver.cc:104 / :405
+    sdf->Init(silhouette.width(), silhouette.height(), 0.0f);
+    out = sdf->data_ptr()->data();
+  }
+  return report(h, vcb_carve_masks(h, 1, &view, &mask, sdf != nullptr ? &out : nullptr),
+                "VoxelCarver::Carve");
+}
+
+bool VoxelCarver::Carve(const Camera& camera, const Eigen::Vector2i& roi_min,
+                        const Eigen::Vector2i& roi_max, const Image1f& sdf) {
+  vcb_carver* h = find_carver(this);
+  if (h == nullptr) {
+    LOGE("VoxelCarver::Carve voxel grid has not been initialized\n");
+    return false;
+  }
+  vcb_view view;
+  if (!make_view(camera, sdf.width(), sdf.height(), roi_min, roi_max, &view)) return false;
+  const float* img = sdf.data().data();
+  return report(h, vcb_carve_sdfs(h, 1, &view, &img), "VoxelCarver::Carve");
+}
+
+bool VoxelCarver::Carve(const Camera& camera, const Image1b& silhouette) {
+  return Carve(camera, silhouette, Eigen::Vector2i(0, 0),
+               Eigen::Vector2i(silhouette.width() - 1, silhouette.height() - 1), nullptr);
+}
+
+bool VoxelCarver::Carve(const Camera& camera, const Image1b& silhouette, Image1f* sdf) {
+  return Carve(camera, silhouette, Eigen::Vector2i(0, 0),
+               Eigen::Vector2i(silhouette.width() - 1, silhouette.height() - 1), sdf);
+}
+
+bool VoxelCarver::Carve(const Camera& camera, const Image1f& sdf) {
+  return Carve(camera, Eigen::Vector2i(0, 0), Eigen::Vector2i(sdf.width() - 1, sdf.height() - 1),
+               sdf);
+}
+
+bool VoxelCarver::Carve(const std::vector<Camera>& cameras,
+                        const std::vector<Image1b>& silhouettes) {
+  assert(cameras.size() == silhouettes.size());
+  for (size_t i = 0; i < cameras.size(); i++) {  // voxel_carver.cc:520-525
+    if (!Carve(cameras[i], silhouettes[i])) return false;
+  }
+  return true;
+}
+
+namespace {
+// Mesh setters deep-copy (mesh.cc:241-271); Vector3f / Vector3i are 3 packed scalars
+void fill_mesh(Mesh* mesh, const std::vector<float>& v, const std::vector<int32_t>& f) {
+  std::vector<Eigen::Vector3f> vertices(v.size() / 3);
+  std::vector<Eigen::Vector3i> faces(f.size() / 3);
+  static_assert(sizeof(Eigen::Vector3f) == 12 && sizeof(Eigen::Vector3i) == 12, "packed");
+  if (!v.empty()) std::memcpy(vertices.data(), v.data(), v.size() * sizeof(float));
+  if (!f.empty()) std::memcpy(faces.data(), f.data(), f.size() * sizeof(int32_t));
+  mesh->set_vertices(vertices);
+  mesh->set_vertex_indices(faces);
+}
+}  // namespace
+
+void VoxelCarver::ExtractVoxel(Mesh* mesh, bool inside_empty) {  // voxel_carver.cc:530-538
+  mesh->Clear();
+  vcb_carver* h = find_carver(this);
+  if (h == nullptr) return;
+  int64_t n = 0;
+  if (!report(h, vcb_extract_voxel_count(h, inside_empty ? 1 : 0, &n), "VoxelCarver::ExtractVoxel")) {
+    return;
+  }
+  std::vector<float> v(static_cast<size_t>(n) * 72);
+  std::vector<int32_t> f(static_cast<size_t>(n) * 36);
+  if (n > 0 && !report(h, vcb_extract_voxel_fill(h, v.data(), f.data()), "VoxelCarver::ExtractVoxel")) {
+    return;
+  }
+  fill_mesh(mesh, v, f);
+}
+
+void VoxelCarver::ExtractIsoSurface(Mesh* mesh, double iso_level, bool linear_interp) {
+  mesh->Clear();  // marching_cubes.cc:68
+  vcb_carver* h = find_carver(this);
+  if (h == nullptr) return;
+  int64_t nv = 0, nf = 0;
+  if (!report(h, vcb_extract_iso_count(h, iso_level, linear_interp ? 1 : 0, &nv, &nf),
+              "VoxelCarver::ExtractIsoSurface")) {
+    return;
+  }
+  std::vector<float> v(static_cast<size_t>(nv) * 3);
+  std::vector<int32_t> f(static_cast<size_t>(nf) * 3);
+  if (!report(h, vcb_extract_iso_fill(h, v.data(), f.data()), "VoxelCarver::ExtractIsoSurface")) {
+    return;
+  }
+  fill_mesh(mesh, v, f);
+}
+
+}  // namespace vacancy
