@@ -143,6 +143,29 @@ int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t 
                                    const int32_t roi_max[2], int32_t minmax_normalize,
                                    int32_t use_truncation, float truncation_band, float* dist);
 
+/* No counterpart in the reference: MakeSignedDistanceField for callers that must not allocate.
+ * Some hosts cannot let a library call cudaMalloc once they are running: an application whose
+ * own arena has claimed the GPU's memory (a driver allocation may then fail, or fragment what is
+ * left), or an acquisition loop that cannot afford the device-wide synchronisation an allocation
+ * implies.  This variant therefore takes the mask and the result as DEVICE pointers supplied by the
+ * caller, works on `cuda_stream` (a cudaStream_t, NULL = default stream) without waiting for it,
+ * and keeps its 4 bytes per pixel of intermediate storage in a fixed array inside the library:
+ *   - limit: width * height <= 2048 * 2048 pixels; larger images are refused with
+ *     VCB_ERR_INVALID (use vcb_make_signed_distance_field for those);
+ *   - cost: every GPU that loads the library holds that array (16 MiB) until the process exits;
+ *   - the array is shared by all calls and keeps the previous call's contents; each call
+ *     re-initialises the cells it accumulates into, but two calls whose kernels overlap on the GPU
+ *     (different streams, or different host threads) race on it - serialise them;
+ *   - the first call on each device looks up the array's device address (a host-side set-up step);
+ *     make that first call before starting any stream capture.
+ * The result equals vcb_make_signed_distance_field bit for bit. It never calls cudaMalloc,
+ * cudaFree or any allocating routine. */
+int vcb_make_signed_distance_field_noalloc(int32_t device, const uint8_t* mask_dev, int32_t width,
+                                           int32_t height, const int32_t roi_min[2],
+                                           const int32_t roi_max[2], int32_t minmax_normalize,
+                                           int32_t use_truncation, float truncation_band,
+                                           float* dist_dev, void* cuda_stream);
+
 /* ExtractIsoSurface(mesh, iso_level, linear_interp), voxel_carver.cc:540-543 ->
  * MarchingCubes marching_cubes.cc:63-228, two-phase: _count runs the extraction on the device and
  * reports the sizes, _fill copies the mesh into HOST buffers (3 floats per vertex, 3 int32 per

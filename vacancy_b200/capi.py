@@ -38,6 +38,7 @@ EXPORTS = [
     "vcb_grid_dims", "vcb_slab_range", "vcb_grid_positions", "vcb_set_stream", "vcb_synchronize",
     "vcb_flush", "vcb_carve_masks", "vcb_carve_masks_device", "vcb_carve_sdfs",
     "vcb_carve_sdfs_device", "vcb_distance_transform_l1", "vcb_make_signed_distance_field",
+    "vcb_make_signed_distance_field_noalloc",
     "vcb_extract_iso_count", "vcb_extract_iso_fill", "vcb_extract_iso_device",
     "vcb_extract_iso_begin", "vcb_extract_iso_vertices", "vcb_extract_iso_export_top",
     "vcb_extract_iso_import_bottom", "vcb_extract_iso_faces", "vcb_halo_device",
@@ -83,6 +84,8 @@ def load_library(path=LIB_PATH):
     L.vcb_distance_transform_l1.argtypes = [i32, u8p, i32, i32, ip, ip, fp]
     L.vcb_make_signed_distance_field.argtypes = [i32, u8p, i32, i32, ip, ip, i32, i32, C.c_float,
                                                  fp]
+    L.vcb_make_signed_distance_field_noalloc.argtypes = [i32, vp, i32, i32, ip, ip, i32, i32,
+                                                         C.c_float, vp, vp]
     L.vcb_extract_iso_count.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
     L.vcb_extract_iso_begin.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
     L.vcb_extract_iso_vertices.argtypes = [vp, i64]

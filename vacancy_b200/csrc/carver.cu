@@ -352,6 +352,10 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
 
 }  // namespace
 
+namespace vcb {
+void set_global_error(const char* text) { g_last_error = text; }
+}  // namespace vcb
+
 extern "C" {
 
 const char* vcb_last_error(const vcb_carver* c) { return c ? c->err.c_str() : g_last_error.c_str(); }

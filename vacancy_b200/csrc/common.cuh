@@ -130,6 +130,9 @@ cudaError_t iso_import_bottom_ids(const GridDesc& g, IsoExtract* st, const int32
 cudaError_t iso_emit_faces(const GridDesc& g, IsoExtract* st, cudaStream_t stream,
                            int64_t* launches);
 
+// text returned by vcb_last_error(NULL) on this thread (for entry points outside carver.cu)
+void set_global_error(const char* text);
+
 void init_mc_tables();  // uploads the constant-memory tables once per device
 
 }  // namespace vcb

@@ -20,6 +20,9 @@
 // Algorithmic bytes: 1 B (mask) + 4 B (float SDF) per pixel; the int16 scratch adds 8 B/pixel of
 // L2-resident traffic (views are processed kSdfSubBatch at a time to keep it there).
 #include <float.h>
+#include <stdio.h>
+
+#include <mutex>
 
 #include "common.cuh"
 
@@ -265,3 +268,101 @@ void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_
 }
 
 }  // namespace vcb
+
+// ------------------------------------------------------------------------------------------------
+// vcb_make_signed_distance_field_noalloc: the 2D SDF of one mask without a single allocation.
+//
+// The three kernels above need 4 bytes of scratch per pixel (two int16 images) plus a small
+// descriptor block.  Here that scratch is this fixed array, part of the library image: every GPU
+// that loads libvacancy_b200.so carries it (16 MiB + 256 B) until the process exits, and images of
+// more than kNoAllocMaxPixels pixels are refused.  All calls share the one array.
+namespace vcb {
+namespace {
+
+constexpr int64_t kNoAllocMaxPixels = 2048LL * 2048LL;
+constexpr size_t kNoAllocHeader = 256;  // SdfView descriptor, abs-max and image-max cells
+constexpr size_t kNoAllocBytes = kNoAllocHeader + 2 * sizeof(int16_t) * kNoAllocMaxPixels;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the
+// real address is asked for once per device (with that device current) and cached here.
+std::mutex g_noalloc_mutex;
+unsigned char* g_noalloc_ptr[64] = {nullptr};
+
+__global__ void sdf_noalloc_set_view_kernel(unsigned char* scratch, SdfView v) {
+  *reinterpret_cast<SdfView*>(scratch) = v;
+}
+
+}  // namespace
+}  // namespace vcb
+
+extern "C" int vcb_make_signed_distance_field_noalloc(
+    int32_t device, const uint8_t* mask_dev, int32_t width, int32_t height,
+    const int32_t roi_min[2], const int32_t roi_max[2], int32_t minmax_normalize,
+    int32_t use_truncation, float truncation_band, float* dist_dev, void* cuda_stream) {
+  using namespace vcb;
+  char msg[256];
+  if (!mask_dev || !dist_dev || !roi_min || !roi_max) {
+    set_global_error("vcb_make_signed_distance_field_noalloc: null argument");
+    return VCB_ERR_INVALID;
+  }
+  if (width < 1 || height < 1 || width > kMaxImageDim || height > kMaxImageDim ||
+      (int64_t)width * height > kNoAllocMaxPixels) {
+    snprintf(msg, sizeof(msg),
+             "vcb_make_signed_distance_field_noalloc: image %d x %d = %lld pixels exceeds the fixed "
+             "scratch of %lld pixels; use vcb_make_signed_distance_field for larger images",
+             width, height, (long long)width * height, (long long)kNoAllocMaxPixels);
+    set_global_error(msg);
+    return VCB_ERR_INVALID;
+  }
+  if (roi_min[0] < 0 || roi_min[1] < 0 || roi_max[0] >= width || roi_max[1] >= height ||
+      roi_min[0] > roi_max[0] || roi_min[1] > roi_max[1]) {
+    set_global_error("vcb_make_signed_distance_field_noalloc: roi outside the image");
+    return VCB_ERR_INVALID;
+  }
+  if (device < 0 || device >= 64) {
+    set_global_error("vcb_make_signed_distance_field_noalloc: device ordinal out of range");
+    return VCB_ERR_INVALID;
+  }
+  cudaError_t e = cudaSetDevice(device);
+  unsigned char* scratch = nullptr;
+  if (e == cudaSuccess) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[device] == nullptr) {  // first call on this device: resolve the symbol
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+      if (e == cudaSuccess) g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+    }
+    scratch = g_noalloc_ptr[device];
+  }
+  if (e != cudaSuccess || scratch == nullptr) {
+    snprintf(msg, sizeof(msg), "vcb_make_signed_distance_field_noalloc: %s", cudaGetErrorString(e));
+    set_global_error(msg);
+    return VCB_ERR_CUDA;
+  }
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  SdfView v;
+  v.mask = mask_dev;
+  v.out = dist_dev;
+  v.rowd = reinterpret_cast<int16_t*>(scratch + kNoAllocHeader);
+  v.cold = v.rowd + kNoAllocMaxPixels;
+  v.absmax = reinterpret_cast<int*>(scratch + 128);      // both cells are re-initialised by
+  v.max_out = reinterpret_cast<float*>(scratch + 192);   // sdf_row_kernel at the start of a call
+  v.width = width;
+  v.height = height;
+  v.rx0 = roi_min[0];
+  v.ry0 = roi_min[1];
+  v.rx1 = roi_max[0];
+  v.ry1 = roi_max[1];
+  sdf_noalloc_set_view_kernel<<<1, 1, 0, stream>>>(scratch, v);
+  launch_sdf2d(reinterpret_cast<const SdfView*>(scratch), &v, 1, kSdfSigned, minmax_normalize,
+               use_truncation, truncation_band, stream, nullptr);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(msg, sizeof(msg), "vcb_make_signed_distance_field_noalloc: %s", cudaGetErrorString(e));
+    set_global_error(msg);
+    return VCB_ERR_CUDA;
+  }
+  return VCB_OK;
+}
