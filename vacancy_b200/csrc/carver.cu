@@ -61,6 +61,7 @@ struct vcb_carver {
   std::vector<float> h_pos[3];
   float2* wtab = nullptr;
   int wtab_n = 0;
+  int64_t max_count = 0;  // upper bound of update_num over the grid (views fused / uploaded)
   bool un_implied = true;  // update_num < 1  <=>  sdf == kVal (true unless a grid was uploaded)
 
   // queued views
@@ -237,9 +238,43 @@ void launch_grid_reset(vcb_carver* c) {
       c->sdf_alloc + (n_sdf / 4) * 4, c->un + (n_un / 4) * 4, (int)(n_sdf % 4), (int)(n_un % 4));
 }
 
+// weighted-average factors by update count, voxel_carver.cc:91-93: {w*float(n), 1/(w*float(n+1))}.
+// The fusion kernel indexes the table with update_num, so it must reach every count a voxel that
+// still takes updates can hold: min(voxel_max_update_num, views applied so far) + 1.
+int ensure_wtab(vcb_carver* c, int64_t needed) {
+  if (needed <= c->wtab_n) return VCB_OK;
+  int64_t n = 512;
+  while (n < needed) n *= 2;
+  std::vector<float2> t((size_t)n);
+  const float w = c->opt.voxel_update_weight;
+  for (int64_t k = 0; k < n; k++) {
+    volatile float wn = w * (float)k;
+    volatile float den = w * (float)(k + 1);
+    volatile float inv = 1.0f / den;
+    t[(size_t)k].x = wn;
+    t[(size_t)k].y = inv;
+  }
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (c->wtab) CU(c, cudaFree(c->wtab));
+  c->wtab = nullptr;
+  c->wtab_n = 0;
+  CU(c, cudaMalloc(&c->wtab, (size_t)n * sizeof(float2)));
+  CU(c, cudaMemcpy(c->wtab, t.data(), (size_t)n * sizeof(float2), cudaMemcpyHostToDevice));
+  c->wtab_n = (int)n;
+  c->fp.wtab = c->wtab;
+  c->fp.wtab_n = c->wtab_n;
+  return VCB_OK;
+}
+
 // launches the fusion kernel over the queued views
 int flush_pending(vcb_carver* c) {
   if (c->pending == 0) return VCB_OK;
+  c->max_count += c->pending;
+  {
+    const int64_t cap = (int64_t)c->opt.voxel_max_update_num + 1;
+    const int rc = ensure_wtab(c, (c->max_count < cap ? c->max_count : cap) + 2);
+    if (rc != VCB_OK) return rc;
+  }
   c->fp.n_views = c->pending;
   {
     Span span(c, 1);
@@ -435,21 +470,6 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
     CREATE_TRY(cudaMalloc(dpos[a], dims[a] * sizeof(float)));
     CREATE_TRY(cudaMemcpy(*dpos[a], c->h_pos[a].data(), dims[a] * sizeof(float), cudaMemcpyHostToDevice));
   }
-  // weighted-average factors by update count, voxel_carver.cc:91-93
-  c->wtab_n = opt->voxel_max_update_num < 4096 ? opt->voxel_max_update_num + 2 : 4098;
-  {
-    std::vector<float2> t(c->wtab_n);
-    const float w = opt->voxel_update_weight;
-    for (int k = 0; k < c->wtab_n; k++) {
-      volatile float wn = w * (float)k;
-      volatile float den = w * (float)(k + 1);
-      volatile float inv = 1.0f / den;
-      t[k].x = wn;
-      t[k].y = inv;
-    }
-    CREATE_TRY(cudaMalloc(&c->wtab, c->wtab_n * sizeof(float2)));
-    CREATE_TRY(cudaMemcpy(c->wtab, t.data(), c->wtab_n * sizeof(float2), cudaMemcpyHostToDevice));
-  }
   CREATE_TRY(c->max_sdf.reserve(sizeof(float) * kMaxViewsPerLaunch));
   // sdf = kVal, update_num = 0 (voxel_carver.cc:342, voxel_carver.h:67-68)
   launch_grid_reset(c);
@@ -461,8 +481,6 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
   c->fp.pos_x = c->pos_x;
   c->fp.pos_y = c->pos_y;
   c->fp.pos_z = c->pos_z;
-  c->fp.wtab = c->wtab;
-  c->fp.wtab_n = c->wtab_n;
   c->fp.nx = c->nx;
   c->fp.ny = c->ny;
   c->fp.z_begin = z0;
@@ -472,6 +490,14 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
   c->fp.update_outside = opt->update_outside;
   c->fp.weight = opt->voxel_update_weight;
 #undef CREATE_TRY
+  {
+    const int64_t cap = (int64_t)opt->voxel_max_update_num + 2;
+    if (ensure_wtab(c, cap < 257 ? cap : 257) != VCB_OK) {
+      g_last_error = c->err;
+      vcb_destroy(c);
+      return VCB_ERR_CUDA;
+    }
+  }
   *out = c;
   return VCB_OK;
 }
@@ -501,6 +527,7 @@ int vcb_reset(vcb_carver* c) {
   int rc = use_device(c, c->opt.device);
   if (rc != VCB_OK) return rc;
   c->pending = 0;  // views queued but not yet fused belong to the grid being discarded
+  c->max_count = 0;
   launch_grid_reset(c);
   c->stage_launches[1] += 1;
   c->un_implied = true;
@@ -865,6 +892,11 @@ int vcb_upload_grid(vcb_carver* c, const float* sdf, const int32_t* update_num) 
   if (update_num)
     CU(c, cudaMemcpyAsync(c->un, update_num, n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
   CU(c, cudaStreamSynchronize(c->stream));
+  if (update_num) {
+    for (size_t i = 0; i < n; i++) {
+      if (update_num[i] > c->max_count) c->max_count = update_num[i];
+    }
+  }
   c->un_implied = false;  // arbitrary state: marching cubes must read update_num itself
   return VCB_OK;
 }
