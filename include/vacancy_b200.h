@@ -149,10 +149,11 @@ int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t 
  * left), or an acquisition loop that cannot afford the device-wide synchronisation an allocation
  * implies.  This variant therefore takes the mask and the result as DEVICE pointers supplied by the
  * caller, works on `cuda_stream` (a cudaStream_t, NULL = default stream) without waiting for it,
- * and keeps its 4 bytes per pixel of intermediate storage in a fixed array inside the library:
- *   - limit: width * height <= 2048 * 2048 pixels; larger images are refused with
- *     VCB_ERR_INVALID (use vcb_make_signed_distance_field for those);
- *   - cost: every GPU that loads the library holds that array (16 MiB) until the process exits;
+ * and keeps its intermediate storage (two int16 images and a bit-plane) in a fixed array inside
+ * the library:
+ *   - limit: W32 * height <= 2048 * 2048 pixels, W32 = width rounded up to a multiple of 32;
+ *     larger images are refused with VCB_ERR_INVALID (use vcb_make_signed_distance_field);
+ *   - cost: every GPU that loads the library holds that array (16.5 MiB) until the process exits;
  *   - the array is shared by all calls and keeps the previous call's contents; each call
  *     re-initialises the cells it accumulates into, but two calls whose kernels overlap on the GPU
  *     (different streams, or different host threads) race on it - serialise them;

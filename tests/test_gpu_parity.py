@@ -293,3 +293,43 @@ def test_slabs_synthetic_vs_oracle(cuda_lib, port):
         for iso in (0.0, 0.03):
             H.assert_mesh_equal(slabs.extract_iso(iso, True), orc.extract_iso(iso, True), o.bb_min,
                                 o.bb_max)
+
+
+def test_cfg2_full_size_against_compiled_reference(cuda_lib, ref):
+    """BASELINE.json config 2 at full size (256^3, 36 views of 1024^2, kMax): 0.6 G voxel-views,
+    every one of them through the shared-reciprocal projection - the fused grid must still equal
+    the UNMODIFIED reference bit for bit, and the mesh must be identical."""
+    cfg = S.CONFIGS["cfg2"]
+    o = S.grid_option(cfg["grid"])
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution)
+    car, rc = make_carver(opt), ref.carver(opt)
+    cams = S.circle_cameras(cfg["views"], cfg["image"], tilt=0.35)
+    masks = [S.silhouette(c, S.DUMBBELL) for c in cams]
+    assert car.carve_batch(cams, masks)
+    for c, m in zip(cams, masks):
+        rc.carve_mask(H.to_oracle_camera(c), m)
+    (gs, gn), (ws, wn) = car.download_grid(), rc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(car.ExtractIsoSurface(), rc.extract_iso(), o.bb_min, o.bb_max)
+    flags, n = car.occupancy(False)
+    assert n == int(((ws <= 0) & (wn >= 1)).sum())
+
+
+def test_cfg3_slab_weighted_against_compiled_reference(cuda_lib, ref):
+    """A 512 x 512 x 48 slab of config 3's grid with 2048^2 views in weighted TSDF mode, 70 views
+    (more than one launch) against the UNMODIFIED reference."""
+    n, planes = 512, 48
+    half = planes / n
+    res = float(np.float32(2.0) / np.float32(n))
+    opt = B.make_options((-1.0, -1.0, -half), (1.0, 1.0, half), res, update=1, truncation=True)
+    car, rc = make_carver(opt), ref.carver(opt)
+    assert car.dims == (n, n, planes)
+    cams = S.circle_cameras(70, 2048, tilt=0.2)
+    mask_cache = {}
+    for i, c in enumerate(cams):
+        m = S.silhouette(c, S.DUMBBELL)
+        assert car.Carve(c, m)
+        rc.carve_mask(H.to_oracle_camera(c), m)
+    (gs, gn), (ws, wn) = car.download_grid(), rc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(car.ExtractIsoSurface(), rc.extract_iso(), opt.bb_min, opt.bb_max)

@@ -4,7 +4,7 @@ It exists for hosts that cannot let a library allocate device memory while they 
 whose own memory arena already owns the GPU (a driver allocation could fail or fragment what is
 left) and capture loops that cannot tolerate the device-wide synchronisation an allocation brings.
 Such a caller hands in device buffers for the mask and the result; the intermediate images live in
-a fixed array inside the library (2048 x 2048 pixels at most).
+a fixed array inside the library (2048 x 2048 pixels at most, the width counted rounded up to 32).
 
 Checked here, through the C ABI, on two calls in a row that reuse that array: the result must be
 bit-identical to the allocating entry point vcb_make_signed_distance_field (the tolerance of every

@@ -71,8 +71,9 @@ struct vcb_carver {
   size_t slot_floats = 0;
   Scratch max_sdf;       // one float per slot
   // 2D SDF scratch
-  Scratch mask_stage, rowd, cold, absmax, sdf_views;
-  size_t sdf_pix = 0;
+  Scratch mask_stage, sdf_scratch, absmax, sdf_views;
+  size_t sdf_pix = 0;      // mask staging bytes per view
+  size_t sdf_scr = 0;      // 2D-SDF scratch bytes per view
 
   VoxelExtract vox;
   IsoExtract iso;
@@ -295,15 +296,18 @@ int ensure_pool(vcb_carver* c, size_t floats_per_image) {
   return VCB_OK;
 }
 
-int ensure_sdf_scratch(vcb_carver* c, size_t pix) {
-  if (pix <= c->sdf_pix && c->rowd.ptr) return VCB_OK;
+int ensure_sdf_scratch(vcb_carver* c, size_t pix, size_t scr) {
+  if (pix <= c->sdf_pix && scr <= c->sdf_scr && c->sdf_scratch.ptr) return VCB_OK;
   CU(c, cudaStreamSynchronize(c->stream));
+  pix = pix > c->sdf_pix ? pix : c->sdf_pix;
+  scr = scr > c->sdf_scr ? scr : c->sdf_scr;
+  pix = (pix + 255) & ~(size_t)255;
   CU(c, c->mask_stage.reserve(pix * kSdfSubBatch));
-  CU(c, c->rowd.reserve(pix * kSdfSubBatch * sizeof(int16_t)));
-  CU(c, c->cold.reserve(pix * kSdfSubBatch * sizeof(int16_t)));
+  CU(c, c->sdf_scratch.reserve(scr * kSdfSubBatch));
   CU(c, c->absmax.reserve(sizeof(int) * kSdfSubBatch));
   CU(c, c->sdf_views.reserve(sizeof(SdfView) * kSdfSubBatch));
   c->sdf_pix = pix;
+  c->sdf_scr = scr;
   return VCB_OK;
 }
 
@@ -314,15 +318,16 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
   if (n_views < 0 || (n_views > 0 && (!views || !masks))) return fail(c, VCB_ERR_INVALID, "null argument");
   int rc = use_device(c, c->opt.device);
   if (rc != VCB_OK) return rc;
-  size_t max_pix = 0;
+  size_t max_pix = 0, max_scr = 0;
   for (int i = 0; i < n_views; i++) {
     if ((rc = check_view(c, views[i])) != VCB_OK) return rc;
     if (!masks[i]) return fail(c, VCB_ERR_INVALID, "mask %d is null", i);
     max_pix = max(max_pix, (size_t)views[i].width * views[i].height);
+    max_scr = max(max_scr, sdf_scratch_bytes(views[i].width, views[i].height));
   }
   if (n_views == 0) return VCB_OK;
   if ((rc = ensure_pool(c, max_pix)) != VCB_OK) return rc;
-  if ((rc = ensure_sdf_scratch(c, max_pix)) != VCB_OK) return rc;
+  if ((rc = ensure_sdf_scratch(c, max_pix, max_scr)) != VCB_OK) return rc;
   float* pool = static_cast<float*>(c->pool.ptr);
   float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
   for (int first = 0; first < n_views;) {
@@ -341,8 +346,7 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
         hv[i].mask = dst;
       }
       hv[i].out = pool + (size_t)slot * c->slot_floats;
-      hv[i].rowd = static_cast<int16_t*>(c->rowd.ptr) + (size_t)i * c->sdf_pix;
-      hv[i].cold = static_cast<int16_t*>(c->cold.ptr) + (size_t)i * c->sdf_pix;
+      hv[i].scratch = static_cast<unsigned char*>(c->sdf_scratch.ptr) + (size_t)i * c->sdf_scr;
       hv[i].absmax = static_cast<int*>(c->absmax.ptr) + i;
       hv[i].max_out = max_sdf + slot;
       hv[i].width = v.width;
@@ -513,7 +517,7 @@ void vcb_destroy(vcb_carver* c) {
   cudaFree(c->pos_y);
   cudaFree(c->pos_z);
   cudaFree(c->wtab);
-  Scratch* all[] = {&c->pool, &c->max_sdf, &c->mask_stage, &c->rowd, &c->cold, &c->absmax,
+  Scratch* all[] = {&c->pool, &c->max_sdf, &c->mask_stage, &c->sdf_scratch, &c->absmax,
                     &c->sdf_views, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
@@ -676,10 +680,9 @@ static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width,
   if ((rc = use_device(nullptr, device)) != VCB_OK) return rc;
   const size_t pix = (size_t)width * height;
   Scratch buf;
-  // layout: float out | int16 rowd | int16 cold | mask | SdfView | int absmax | float max
-  const size_t off_rowd = pix * sizeof(float);
-  const size_t off_cold = off_rowd + pix * sizeof(int16_t);
-  const size_t off_mask = off_cold + pix * sizeof(int16_t);
+  // layout: float out | kernel scratch | mask | SdfView | int absmax | float max
+  const size_t off_scr = (pix * sizeof(float) + 255) & ~(size_t)255;
+  const size_t off_mask = off_scr + sdf_scratch_bytes(width, height);
   const size_t off_view = (off_mask + pix + 255) / 256 * 256;
   const size_t off_misc = off_view + 256;
   CU(nullptr, buf.reserve(off_misc + 256));
@@ -687,8 +690,7 @@ static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width,
   SdfView hv;
   hv.mask = reinterpret_cast<uint8_t*>(base + off_mask);
   hv.out = reinterpret_cast<float*>(base);
-  hv.rowd = reinterpret_cast<int16_t*>(base + off_rowd);
-  hv.cold = reinterpret_cast<int16_t*>(base + off_cold);
+  hv.scratch = reinterpret_cast<unsigned char*>(base + off_scr);
   hv.absmax = reinterpret_cast<int*>(base + off_misc);
   hv.max_out = reinterpret_cast<float*>(base + off_misc + 64);
   hv.width = width;

@@ -56,8 +56,7 @@ struct FuseParams {
 struct SdfView {
   const uint8_t* mask;   // device, width x height
   float* out;            // device float image
-  int16_t* rowd;         // scratch: signed row distance
-  int16_t* cold;         // scratch: signed L1 distance
+  unsigned char* scratch;  // sdf_scratch_bytes(width, height) bytes, 256-byte aligned
   int* absmax;           // scratch: [0] max |D| over the ROI (INT_MAX when some pixel has no seed)
   float* max_out;        // device scalar: max over the final float image
   int width, height;
@@ -65,6 +64,8 @@ struct SdfView {
 };
 
 enum SdfMode { kSdfSigned = 0, kSdfDistanceL1 = 1 };
+
+size_t sdf_scratch_bytes(int width, int height);  // per-view scratch of the 2D SDF kernels
 
 void launch_sdf2d(const SdfView* views_dev, const SdfView* views_host, int n_views, int mode,
                   int normalize, int truncate, float band, cudaStream_t stream, int64_t* launches);

@@ -8,10 +8,11 @@
 // Distances are integers <= width + height - 2, so the passes run in int16/int32 and the float
 // image produced at the end is bit-identical to the reference's.
 //
-//   sdf_row_kernel : one warp per ROI row; 32-pixel chunks, ballot + clz/ffs give the nearest
-//                    opposite-class pixel to the left (forward sweep) and right (backward sweep).
-//                    Output: signed row distance (fg negative, bg positive), kRowInf = none.
-//   sdf_col_kernel : one block per 32 columns x 32 row segments; prefix-min of (g(y') - y') and
+//   sdf_bits_kernel: the foreground bit-plane (1 bit per pixel, ROI applied), 32 pixels per thread.
+//   sdf_row_kernel : one warp per ROI row, one lane per 32-pixel word: warp max/min scans carry the
+//                    nearest foreground / background pixel across words, clz/ffs resolve it inside a
+//                    word.  Output: signed row distance (fg negative, bg positive), kRowInf = none.
+//   sdf_col_kernel : one block per 32 columns x 8 row segments; prefix-min of (g(y') - y') and
 //                    suffix-min of (g(y') + y') per segment, carries exchanged through shared memory,
 //                    for both polarities at once.  Output: signed L1 distance + max |D| (atomic).
 //   sdf_finalize_kernel : int -> float, whole-image min/max normalisation (:205-222), truncation
@@ -28,7 +29,28 @@
 
 namespace vcb {
 
+// Per-view scratch: two int16 images with the row pitch rounded up to 32 pixels (so that every
+// scratch access is aligned whatever the image width) and one bit per pixel.
+__host__ __device__ inline int sdf_pitch(int width) { return (width + 31) & ~31; }
+__host__ __device__ inline size_t sdf_plane_bytes(int width, int height) {
+  return ((size_t)sdf_pitch(width) * height * sizeof(int16_t) + 255) & ~(size_t)255;
+}
+size_t sdf_scratch_bytes(int width, int height) {
+  const size_t bits = ((size_t)(sdf_pitch(width) / 32) * height * sizeof(uint32_t) + 255) & ~(size_t)255;
+  return 2 * sdf_plane_bytes(width, height) + bits;
+}
+
 namespace {
+
+__device__ __forceinline__ int16_t* view_rowd(const SdfView& v) {
+  return reinterpret_cast<int16_t*>(v.scratch);
+}
+__device__ __forceinline__ int16_t* view_cold(const SdfView& v) {
+  return reinterpret_cast<int16_t*>(v.scratch + sdf_plane_bytes(v.width, v.height));
+}
+__device__ __forceinline__ uint32_t* view_bits(const SdfView& v) {
+  return reinterpret_cast<uint32_t*>(v.scratch + 2 * sdf_plane_bytes(v.width, v.height));
+}
 
 __device__ __forceinline__ float atomic_max_float(float* addr, float value) {
   return value >= 0.0f
@@ -37,82 +59,179 @@ __device__ __forceinline__ float atomic_max_float(float* addr, float value) {
                    atomicMin(reinterpret_cast<unsigned*>(addr), __float_as_uint(value)));
 }
 
-constexpr int kRowWarps = 8;
+// bits [lo, hi] (inclusive) of a 32-bit word whose bit 0 is pixel x0; empty when out of range
+__device__ __forceinline__ unsigned roi_word_mask(int x0, int rx0, int rx1) {
+  const int lo = max(rx0 - x0, 0), hi = min(rx1 - x0, 31);
+  if (lo > 31 || hi < 0 || lo > hi) return 0u;
+  return (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
+}
 
-__global__ void __launch_bounds__(kRowWarps * 32) sdf_row_kernel(const SdfView* __restrict__ views) {
+// ---- pass 0: foreground bit-plane. One thread per 32-pixel word of a ROI row. -------------------
+// Only the value 255 is foreground (voxel_carver.cc:109).
+__global__ void __launch_bounds__(256) sdf_bits_kernel(const SdfView* __restrict__ views) {
   const SdfView v = views[blockIdx.y];
-  const int lane = threadIdx.x & 31;
-  const int warp = blockIdx.x * kRowWarps + (threadIdx.x >> 5);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     *v.absmax = 0;
     *v.max_out = -FLT_MAX;
   }
-  const int y = v.ry0 + warp;
-  if (y > v.ry1) return;
-  const uint8_t* __restrict__ m = v.mask + (size_t)y * v.width;
-  int16_t* __restrict__ r = v.rowd + (size_t)y * v.width;
-  constexpr int kFar = 1 << 20;
-  const unsigned lt_mask = (1u << lane) - 1u;
-  const unsigned gt_mask = ~((2u << lane) - 1u);
-
-  int last_f = -kFar, last_b = -kFar;
-  const int n_chunks = (v.rx1 - v.rx0) / 32 + 1;
-  for (int c = 0; c < n_chunks; c++) {
-    const int x0 = v.rx0 + c * 32;
-    const int x = x0 + lane;
-    const bool in = x <= v.rx1;
-    const bool fg = in && (m[x] == 255);  // only 255 is foreground, voxel_carver.cc:109
-    const unsigned fgb = __ballot_sync(0xffffffffu, fg);
-    const unsigned bgb = __ballot_sync(0xffffffffu, in) & ~fgb;
-    const unsigned left = (fg ? bgb : fgb) & lt_mask;
-    const int xl = left ? (x0 + 31 - __clz(left)) : (fg ? last_b : last_f);
-    const int dl = x - xl;
-    if (in) r[x] = (int16_t)(dl > 32766 ? kRowInf : dl);
-    if (fgb) last_f = x0 + 31 - __clz(fgb);
-    if (bgb) last_b = x0 + 31 - __clz(bgb);
-  }
-  int next_f = 2 * kFar, next_b = 2 * kFar;
-  for (int c = n_chunks - 1; c >= 0; c--) {
-    const int x0 = v.rx0 + c * 32;
-    const int x = x0 + lane;
-    const bool in = x <= v.rx1;
-    const bool fg = in && (m[x] == 255);
-    const unsigned fgb = __ballot_sync(0xffffffffu, fg);
-    const unsigned bgb = __ballot_sync(0xffffffffu, in) & ~fgb;
-    const unsigned right = (fg ? bgb : fgb) & gt_mask;
-    const int xr = right ? (x0 + __ffs(right) - 1) : (fg ? next_b : next_f);
-    if (in) {
-      int d = min((int)r[x], xr - x);
-      if (d > 32766) d = kRowInf;
-      r[x] = (int16_t)(fg ? -d : d);
+  const int wpr = sdf_pitch(v.width) / 32;
+  const int rows = v.ry1 - v.ry0 + 1;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rows * wpr) return;
+  const int y = v.ry0 + idx / wpr, w = idx % wpr;
+  const int x0 = w * 32;
+  const uint8_t* __restrict__ m = v.mask + (size_t)y * v.width + x0;
+  unsigned f = 0;
+  if ((v.width & 3) == 0 && x0 + 32 <= v.width) {
+    // byte == 0xFF  <=>  bit 7 set and the low 7 bits + 1 carry into bit 7; gather the four flags
+    const uint32_t* __restrict__ m4 = reinterpret_cast<const uint32_t*>(m);
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const unsigned q = __ldg(m4 + i);
+      const unsigned t = ((q & 0x7f7f7f7fu) + 0x01010101u) & q & 0x80808080u;
+      f |= ((((t >> 7) * 0x00204081u) >> 21) & 0xfu) << (4 * i);
     }
-    if (fgb) next_f = x0 + __ffs(fgb) - 1;
-    if (bgb) next_b = x0 + __ffs(bgb) - 1;
+  } else {
+    for (int i = 0; i < 32; i++) {
+      if (x0 + i < v.width && m[i] == 255) f |= 1u << i;
+    }
+  }
+  view_bits(v)[(size_t)y * wpr + w] = f & roi_word_mask(x0, v.rx0, v.rx1);
+}
+
+// ---- pass 1: signed distance along the row. One warp per ROI row, one lane per 32-pixel word. ---
+// For every ROI pixel: distance to the nearest pixel of the OTHER class in its row (inside the ROI):
+// negative on foreground, positive on background, +-kRowInf when the row has none.
+constexpr int kRowWarps = 8;
+constexpr int kMaxWordsPerRow = kMaxImageDim / 32;
+
+__global__ void __launch_bounds__(kRowWarps * 32) sdf_row_kernel(const SdfView* __restrict__ views) {
+  const SdfView v = views[blockIdx.y];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int y = v.ry0 + blockIdx.x * kRowWarps + wib;
+  if (y > v.ry1) return;
+  const int pitch = sdf_pitch(v.width), wpr = pitch / 32;
+  const uint32_t* __restrict__ bits = view_bits(v) + (size_t)y * wpr;
+  int16_t* __restrict__ out = view_rowd(v) + (size_t)y * pitch;
+  const int w0 = v.rx0 >> 5, w1 = v.rx1 >> 5;
+  constexpr int kFar = 1 << 20;
+  // position of the last foreground / background pixel strictly before each word
+  __shared__ int s_last_f[kRowWarps][kMaxWordsPerRow], s_last_b[kRowWarps][kMaxWordsPerRow];
+
+  int carry_f = -kFar, carry_b = -kFar;
+  for (int wb = w0; wb <= w1; wb += 32) {
+    const int w = wb + lane;
+    const bool ok = w <= w1;
+    const unsigned vm = ok ? roi_word_mask(w * 32, v.rx0, v.rx1) : 0u;
+    const unsigned fw = ok ? bits[w] : 0u, bw = ~fw & vm;
+    int hf = fw ? w * 32 + 31 - __clz(fw) : -kFar;
+    int hb = bw ? w * 32 + 31 - __clz(bw) : -kFar;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {  // inclusive max-scan over the lanes
+      const int tf = __shfl_up_sync(0xffffffffu, hf, o), tb = __shfl_up_sync(0xffffffffu, hb, o);
+      if (lane >= o) {
+        hf = max(hf, tf);
+        hb = max(hb, tb);
+      }
+    }
+    int ef = __shfl_up_sync(0xffffffffu, hf, 1), eb = __shfl_up_sync(0xffffffffu, hb, 1);
+    if (lane == 0) {
+      ef = -kFar;
+      eb = -kFar;
+    }
+    if (ok) {
+      s_last_f[wib][w - w0] = max(carry_f, ef);
+      s_last_b[wib][w - w0] = max(carry_b, eb);
+    }
+    carry_f = max(carry_f, __shfl_sync(0xffffffffu, hf, 31));
+    carry_b = max(carry_b, __shfl_sync(0xffffffffu, hb, 31));
+  }
+  __syncwarp();
+  carry_f = 2 * kFar;  // now: first foreground / background pixel strictly after the word
+  carry_b = 2 * kFar;
+  const int n_chunks = (w1 - w0) / 32 + 1;
+  for (int c = n_chunks - 1; c >= 0; c--) {
+    const int w = w0 + c * 32 + lane;
+    const bool ok = w <= w1;
+    const unsigned vm = ok ? roi_word_mask(w * 32, v.rx0, v.rx1) : 0u;
+    const unsigned fw = ok ? bits[w] : 0u, bw = ~fw & vm;
+    int lf = fw ? w * 32 + __ffs(fw) - 1 : 2 * kFar;
+    int lb = bw ? w * 32 + __ffs(bw) - 1 : 2 * kFar;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {  // inclusive min-scan from the high lanes down
+      const int tf = __shfl_down_sync(0xffffffffu, lf, o), tb = __shfl_down_sync(0xffffffffu, lb, o);
+      if (lane + o < 32) {
+        lf = min(lf, tf);
+        lb = min(lb, tb);
+      }
+    }
+    int nf = __shfl_down_sync(0xffffffffu, lf, 1), nb = __shfl_down_sync(0xffffffffu, lb, 1);
+    if (lane == 31) {
+      nf = 2 * kFar;
+      nb = 2 * kFar;
+    }
+    nf = min(nf, carry_f);
+    nb = min(nb, carry_b);
+    carry_f = min(carry_f, __shfl_sync(0xffffffffu, lf, 0));
+    carry_b = min(carry_b, __shfl_sync(0xffffffffu, lb, 0));
+    if (ok) {
+      const int pf = s_last_f[wib][w - w0], pb = s_last_b[wib][w - w0];
+      const int xb = w * 32;
+      uint32_t packed[16];
+#pragma unroll
+      for (int i = 0; i < 32; i++) {
+        const bool fg = (fw >> i) & 1u;
+        const unsigned opp = fg ? bw : fw;  // the other class
+        const unsigned lo = opp & ((2u << i) - 1u), hi = opp >> i;
+        const int x = xb + i;
+        const int dl = lo ? i - (31 - __clz(lo)) : x - (fg ? pb : pf);
+        const int dr = hi ? __ffs(hi) - 1 : (fg ? nb : nf) - x;
+        int d = min(min(dl, dr), (int)kRowInf);
+        d = ((vm >> i) & 1u) ? (fg ? -d : d) : 0;
+        if (i & 1) {
+          packed[i >> 1] |= (uint32_t)(uint16_t)d << 16;
+        } else {
+          packed[i >> 1] = (uint32_t)(uint16_t)d;
+        }
+      }
+      uint4* dst = reinterpret_cast<uint4*>(out + xb);
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        dst[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+      }
+    }
   }
 }
 
+// ---- pass 2: combine along the column. Block = 32 columns x kColSegs row segments. --------------
+// D(x, y) = min over y' of |y - y'| + g(x, y'), g = 0 on pixels of the other class, the row distance
+// elsewhere: prefix-min of (g - y') and suffix-min of (g + y') per segment, carries through shared
+// memory, for the distance-to-background (a) and distance-to-foreground (b) transforms at once.
 constexpr int kColInf = 1 << 28;
+constexpr int kColSegs = 32;
 
-__global__ void __launch_bounds__(1024) sdf_col_kernel(const SdfView* __restrict__ views) {
+__global__ void __launch_bounds__(32 * kColSegs) sdf_col_kernel(const SdfView* __restrict__ views) {
   const SdfView v = views[blockIdx.y];
   const int cx = threadIdx.x, seg = threadIdx.y;
   const int x = v.rx0 + blockIdx.x * 32 + cx;
   const bool col_ok = x <= v.rx1;
   const int roi_h = v.ry1 - v.ry0 + 1;
-  const int seglen = (roi_h + 31) / 32;
+  const int seglen = (roi_h + kColSegs - 1) / kColSegs;
   const int ys = v.ry0 + seg * seglen;
   const int ye = min(ys + seglen, v.ry1 + 1);
-  const int W = v.width;
+  const int pitch = sdf_pitch(v.width);
+  const int16_t* __restrict__ rowd = view_rowd(v);
+  int16_t* __restrict__ cold = view_cold(v);
 
-  __shared__ int s_pa[32][33], s_qa[32][33], s_pb[32][33], s_qb[32][33];
+  __shared__ int s_pa[kColSegs][33], s_qa[kColSegs][33], s_pb[kColSegs][33], s_qb[kColSegs][33];
 
-  // phase 1: per-segment prefix / suffix seeds for both polarities
   int pa = kColInf, qa = kColInf, pb = kColInf, qb = kColInf;
   if (col_ok) {
+#pragma unroll 8
     for (int y = ys; y < ye; y++) {
-      const int r = v.rowd[(size_t)y * W + x];
-      const int ga = r < 0 ? (r == -kRowInf ? kColInf : -r) : 0;  // distance-to-background seeds
-      const int gb = r > 0 ? (r == kRowInf ? kColInf : r) : 0;    // distance-to-foreground seeds
+      const int r = __ldg(rowd + (size_t)y * pitch + x);
+      const int ga = r < 0 ? (r == -kRowInf ? kColInf : -r) : 0;
+      const int gb = r > 0 ? (r == kRowInf ? kColInf : r) : 0;
       pa = min(pa, ga - y);
       qa = min(qa, ga + y);
       pb = min(pb, gb - y);
@@ -124,58 +243,147 @@ __global__ void __launch_bounds__(1024) sdf_col_kernel(const SdfView* __restrict
   s_pb[seg][cx] = pb;
   s_qb[seg][cx] = qb;
   __syncthreads();
-  // phase 2: carries from the other segments of this column
   int cpa = kColInf, cpb = kColInf, cqa = kColInf, cqb = kColInf;
   for (int s = 0; s < seg; s++) {
     cpa = min(cpa, s_pa[s][cx]);
     cpb = min(cpb, s_pb[s][cx]);
   }
-  for (int s = seg + 1; s < 32; s++) {
+  for (int s = seg + 1; s < kColSegs; s++) {
     cqa = min(cqa, s_qa[s][cx]);
     cqb = min(cqb, s_qb[s][cx]);
   }
-  // phase 3: forward then backward over the segment
   int local_max = 0;
   if (col_ok) {
     int ra = cpa, rb = cpb;
+#pragma unroll 8
     for (int y = ys; y < ye; y++) {
-      const size_t i = (size_t)y * W + x;
-      const int r = v.rowd[i];
+      const size_t i = (size_t)y * pitch + x;
+      const int r = __ldg(rowd + i);
       const int ga = r < 0 ? (r == -kRowInf ? kColInf : -r) : 0;
       const int gb = r > 0 ? (r == kRowInf ? kColInf : r) : 0;
       ra = min(ra, ga - y);
       rb = min(rb, gb - y);
       const int f = (r < 0 ? ra : rb) + y;
-      v.cold[i] = (int16_t)(f > 32766 ? kRowInf : f);
+      cold[i] = (int16_t)(f > 32766 ? kRowInf : f);
     }
     ra = cqa;
     rb = cqb;
+#pragma unroll 8
     for (int y = ye - 1; y >= ys; y--) {
-      const size_t i = (size_t)y * W + x;
-      const int r = v.rowd[i];
+      const size_t i = (size_t)y * pitch + x;
+      const int r = __ldg(rowd + i);
       const int ga = r < 0 ? (r == -kRowInf ? kColInf : -r) : 0;
       const int gb = r > 0 ? (r == kRowInf ? kColInf : r) : 0;
       ra = min(ra, ga + y);
       rb = min(rb, gb + y);
-      int d = min((int)v.cold[i], (r < 0 ? ra : rb) - y);
+      int d = min((int)cold[i], (r < 0 ? ra : rb) - y);
       if (d > 32766) {
         d = kRowInf;
         local_max = INT_MAX;
       } else {
         local_max = max(local_max, d);
       }
-      v.cold[i] = (int16_t)(r < 0 ? -d : d);
+      cold[i] = (int16_t)(r < 0 ? -d : d);
     }
   }
   local_max = __reduce_max_sync(0xffffffffu, local_max);
   if (cx == 0 && local_max > 0) atomicMax(v.absmax, local_max);
 }
 
+// Same pass with the block's 32-column strip staged in shared memory (up to 32 x 3168 int16).
+// Seeds need no special "infinite" value here: a row distance of kRowInf (32767) exceeds every
+// finite L1 distance (<= width + height - 2 <= 32766), so a result >= 32767 simply means "no seed".
+// Recurrences: forward f(y) = min(f(y-1) + 1, g(y)), backward b(y) = min(b(y+1) + 1, g(y)), each one
+// fused add-min per polarity; carries between the 32 row segments go through shared memory.
+constexpr int kColMaxSegLen = 99;  // 32 cols * 32 segs * 99 rows * 2 B = 198 KB (+17 KB of carries)
+constexpr int kColFar = 1 << 20;
+
+__global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const SdfView* __restrict__ views) {
+  const SdfView v = views[blockIdx.y];
+  const int cx = threadIdx.x, seg = threadIdx.y;
+  const int x = v.rx0 + blockIdx.x * 32 + cx;
+  if (v.rx0 + blockIdx.x * 32 > v.rx1) return;  // whole block outside this view's ROI
+  const bool col_ok = x <= v.rx1;
+  const int roi_h = v.ry1 - v.ry0 + 1;
+  const int seglen = (roi_h + 31) / 32;
+  const int ys = v.ry0 + seg * seglen;
+  const int rows = max(0, min(seglen, v.ry1 + 1 - ys));
+  const int pitch = sdf_pitch(v.width);
+  const int16_t* __restrict__ rowd = view_rowd(v) + (size_t)ys * pitch + x;
+  int16_t* __restrict__ cold = view_cold(v) + (size_t)ys * pitch + x;
+
+  extern __shared__ int16_t s_tile[];                       // [seg][row][cx]
+  // per (segment, column): forward value at the segment's last row / backward value at its first
+  // row, each computed from the segment's own seeds only, for both polarities
+  __shared__ int s_fa[32][33], s_fb[32][33], s_ba[32][33], s_bb[32][33];
+  int16_t* mine = s_tile + (size_t)seg * seglen * 32 + cx;  // stride 32 between rows
+
+  int fa = kColFar, fb = kColFar, ba = kColFar, bb = kColFar;
+  if (col_ok) {
+#pragma unroll 8
+    for (int i = 0; i < rows; i++) {
+      const int r = __ldg(rowd + (size_t)i * pitch);
+      mine[i * 32] = (int16_t)r;
+      const int ga = max(-r, 0), gb = max(r, 0);  // seeds: 0 on the other class, row distance else
+      fa = min(fa + 1, ga);
+      fb = min(fb + 1, gb);
+      ba = min(ba, ga + i);
+      bb = min(bb, gb + i);
+    }
+  }
+  s_fa[seg][cx] = fa;
+  s_fb[seg][cx] = fb;
+  s_ba[seg][cx] = ba;
+  s_bb[seg][cx] = bb;
+  __syncthreads();
+  // carry-in: value of the forward recurrence just above the segment / backward just below it
+  int cfa = kColFar, cfb = kColFar, cba = kColFar, cbb = kColFar;
+  for (int s = 0; s < seg; s++) {  // rows between segment s's last row and ys - 1
+    const int gap = (seg - 1 - s) * seglen;
+    cfa = min(cfa, s_fa[s][cx] + gap);
+    cfb = min(cfb, s_fb[s][cx] + gap);
+  }
+  for (int s = seg + 1; s < 32; s++) {  // rows between this segment's last row + 1 and s's first
+    const int gap = (s - seg - 1) * seglen + (seglen - rows);
+    cba = min(cba, s_ba[s][cx] + gap);
+    cbb = min(cbb, s_bb[s][cx] + gap);
+  }
+  int local_max = 0;
+  if (col_ok) {
+    // backward sweep: b replaces the seed in the strip, the sign keeps the pixel's class
+    ba = cba;
+    bb = cbb;
+    for (int i = rows - 1; i >= 0; i--) {
+      const int r = mine[i * 32];
+      ba = min(ba + 1, max(-r, 0));
+      bb = min(bb + 1, max(r, 0));
+      const int b = min(r < 0 ? ba : bb, (int)kRowInf);
+      mine[i * 32] = (int16_t)(r < 0 ? -b : b);
+    }
+    // forward sweep: seeds again from global memory (L2-hot), min with b, emit
+    fa = cfa;
+    fb = cfb;
+#pragma unroll 8
+    for (int i = 0; i < rows; i++) {
+      const int r = __ldg(rowd + (size_t)i * pitch);
+      const int b = mine[i * 32];
+      fa = min(fa + 1, max(-r, 0));
+      fb = min(fb + 1, max(r, 0));
+      const int d = min(min(r < 0 ? fa : fb, abs(b)), (int)kRowInf);
+      local_max = max(local_max, d);
+      cold[(size_t)i * pitch] = (int16_t)(r < 0 ? -d : d);
+    }
+  }
+  if (local_max >= kRowInf) local_max = INT_MAX;
+  local_max = __reduce_max_sync(0xffffffffu, local_max);
+  if (cx == 0 && local_max > 0) atomicMax(v.absmax, local_max);
+}
+
+// ---- pass 3: int -> float, normalisation, truncation, image maximum. Block per group of rows. ---
 __global__ void __launch_bounds__(256) sdf_finalize_kernel(const SdfView* __restrict__ views,
                                                            int mode, int normalize, int truncate,
                                                            float band) {
   const SdfView v = views[blockIdx.y];
-  const int64_t n = (int64_t)v.width * v.height;
   float norm = 1.0f;
   bool do_norm = false;
   if (normalize && mode == kSdfSigned) {
@@ -186,30 +394,33 @@ __global__ void __launch_bounds__(256) sdf_finalize_kernel(const SdfView* __rest
       norm = __fdiv_rn(1.0f, am);
     }
   }
+  const int pitch = sdf_pitch(v.width);
+  const int16_t* __restrict__ cold = view_cold(v);
   float tmax = -FLT_MAX;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int x = (int)(i % v.width), y = (int)(i / v.width);
-    float f = 0.0f;  // outside the ROI, voxel_carver.cc:104
-    if (x >= v.rx0 && x <= v.rx1 && y >= v.ry0 && y <= v.ry1) {
-      const int d = v.cold[i];
-      if (mode == kSdfSigned) {
-        f = d == kRowInf ? FLT_MAX : (d == -kRowInf ? -FLT_MAX : (float)d);
-        if (do_norm) f = __fmul_rn(f, norm);
-        if (truncate) {  // voxel_carver.cc:225-236
-          if (-band >= f) {
-            f = kInvalidSdf;
-          } else {
-            const float q = __fdiv_rn(f, band);
-            f = q < 1.0f ? q : 1.0f;
+  for (int y = blockIdx.x; y < v.height; y += gridDim.x) {
+    const bool row_in = y >= v.ry0 && y <= v.ry1;
+    for (int x = threadIdx.x; x < v.width; x += blockDim.x) {
+      float f = 0.0f;  // outside the ROI, voxel_carver.cc:104
+      if (row_in && x >= v.rx0 && x <= v.rx1) {
+        const int d = __ldg(cold + (size_t)y * pitch + x);
+        if (mode == kSdfSigned) {
+          f = d == kRowInf ? FLT_MAX : (d == -kRowInf ? -FLT_MAX : (float)d);
+          if (do_norm) f = __fmul_rn(f, norm);
+          if (truncate) {  // voxel_carver.cc:225-236
+            if (-band >= f) {
+              f = kInvalidSdf;
+            } else {
+              const float q = __fdiv_rn(f, band);
+              f = q < 1.0f ? q : 1.0f;
+            }
           }
+        } else {  // DistanceTransformL1 of the mask itself: foreground distance, others 0
+          f = d < 0 ? (d == -kRowInf ? FLT_MAX : (float)(-d)) : 0.0f;
         }
-      } else {  // DistanceTransformL1 of the mask itself: foreground distance, others 0
-        f = d < 0 ? (d == -kRowInf ? FLT_MAX : (float)(-d)) : 0.0f;
       }
+      v.out[(size_t)y * v.width + x] = f;
+      tmax = fmaxf(tmax, f);
     }
-    v.out[i] = f;
-    tmax = fmaxf(tmax, f);
   }
   for (int o = 16; o > 0; o >>= 1) tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
   if ((threadIdx.x & 31) == 0) atomic_max_float(v.max_out, tmax);
@@ -237,24 +448,35 @@ __global__ void set_float_kernel(float* p, float v) { *p = v; }
 void launch_sdf2d(const SdfView* views_dev, const SdfView* views_host, int n_views, int mode,
                   int normalize, int truncate, float band, cudaStream_t stream,
                   int64_t* launches) {
-  int max_rows = 0, max_cols = 0;
-  int64_t max_pix = 0;
+  int max_rows = 0, max_cols = 0, max_h = 0, max_words = 0;
   for (int i = 0; i < n_views; i++) {
     const SdfView& v = views_host[i];
     max_rows = max(max_rows, v.ry1 - v.ry0 + 1);
     max_cols = max(max_cols, v.rx1 - v.rx0 + 1);
-    max_pix = max(max_pix, (int64_t)v.width * v.height);
+    max_h = max(max_h, v.height);
+    max_words = max(max_words, (v.ry1 - v.ry0 + 1) * (sdf_pitch(v.width) / 32));
   }
-  dim3 grow((max_rows + kRowWarps - 1) / kRowWarps, n_views);
-  sdf_row_kernel<<<grow, kRowWarps * 32, 0, stream>>>(views_dev);
-  dim3 gcol((max_cols + 31) / 32, n_views);
-  sdf_col_kernel<<<gcol, dim3(32, 32), 0, stream>>>(views_dev);
-  int64_t fblocks = (max_pix + 256 * 8 - 1) / (256 * 8);
-  if (fblocks < 1) fblocks = 1;
-  if (fblocks > 4096) fblocks = 4096;
-  dim3 gfin((unsigned)fblocks, n_views);
-  sdf_finalize_kernel<<<gfin, 256, 0, stream>>>(views_dev, mode, normalize, truncate, band);
-  if (launches) *launches += 3;
+  sdf_bits_kernel<<<dim3((max_words + 255) / 256, n_views), 256, 0, stream>>>(views_dev);
+  sdf_row_kernel<<<dim3((max_rows + kRowWarps - 1) / kRowWarps, n_views), kRowWarps * 32, 0,
+                   stream>>>(views_dev);
+  const int max_seglen = (max_rows + 31) / 32;
+  if (max_seglen <= kColMaxSegLen) {
+    const size_t smem = (size_t)32 * 32 * max_seglen * sizeof(int16_t);
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      cudaFuncSetAttribute(sdf_col_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           32 * 32 * kColMaxSegLen * (int)sizeof(int16_t));
+      attr_set[dev] = true;
+    }
+    sdf_col_smem_kernel<<<dim3((max_cols + 31) / 32, n_views), dim3(32, 32), smem, stream>>>(views_dev);
+  } else {
+    sdf_col_kernel<<<dim3((max_cols + 31) / 32, n_views), dim3(32, kColSegs), 0, stream>>>(views_dev);
+  }
+  sdf_finalize_kernel<<<dim3(min(max_h, 1024), n_views), 256, 0, stream>>>(views_dev, mode,
+                                                                            normalize, truncate, band);
+  if (launches) *launches += 4;
 }
 
 void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_t stream,
@@ -274,14 +496,17 @@ void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_
 //
 // The three kernels above need 4 bytes of scratch per pixel (two int16 images) plus a small
 // descriptor block.  Here that scratch is this fixed array, part of the library image: every GPU
-// that loads libvacancy_b200.so carries it (16 MiB + 256 B) until the process exits, and images of
-// more than kNoAllocMaxPixels pixels are refused.  All calls share the one array.
+// that loads libvacancy_b200.so carries it (16.5 MiB) until the process exits, and images of more
+// than kNoAllocMaxPixels pixels (width rounded up to a multiple of 32) are refused.  All calls
+// share the one array.
 namespace vcb {
 namespace {
 
-constexpr int64_t kNoAllocMaxPixels = 2048LL * 2048LL;
+constexpr int64_t kNoAllocMaxPixels = 2048LL * 2048LL;  // counted with the width rounded up to 32
 constexpr size_t kNoAllocHeader = 256;  // SdfView descriptor, abs-max and image-max cells
-constexpr size_t kNoAllocBytes = kNoAllocHeader + 2 * sizeof(int16_t) * kNoAllocMaxPixels;
+// two int16 images + one bit per pixel + their 256-byte alignment slack
+constexpr size_t kNoAllocBytes =
+    kNoAllocHeader + 2 * sizeof(int16_t) * kNoAllocMaxPixels + kNoAllocMaxPixels / 8 + 3 * 256;
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
 
@@ -308,7 +533,7 @@ extern "C" int vcb_make_signed_distance_field_noalloc(
     return VCB_ERR_INVALID;
   }
   if (width < 1 || height < 1 || width > kMaxImageDim || height > kMaxImageDim ||
-      (int64_t)width * height > kNoAllocMaxPixels) {
+      (int64_t)sdf_pitch(width) * height > kNoAllocMaxPixels) {
     snprintf(msg, sizeof(msg),
              "vcb_make_signed_distance_field_noalloc: image %d x %d = %lld pixels exceeds the fixed "
              "scratch of %lld pixels; use vcb_make_signed_distance_field for larger images",
@@ -345,10 +570,9 @@ extern "C" int vcb_make_signed_distance_field_noalloc(
   SdfView v;
   v.mask = mask_dev;
   v.out = dist_dev;
-  v.rowd = reinterpret_cast<int16_t*>(scratch + kNoAllocHeader);
-  v.cold = v.rowd + kNoAllocMaxPixels;
+  v.scratch = scratch + kNoAllocHeader;
   v.absmax = reinterpret_cast<int*>(scratch + 128);      // both cells are re-initialised by
-  v.max_out = reinterpret_cast<float*>(scratch + 192);   // sdf_row_kernel at the start of a call
+  v.max_out = reinterpret_cast<float*>(scratch + 192);   // sdf_bits_kernel at the start of a call
   v.width = width;
   v.height = height;
   v.rx0 = roi_min[0];
