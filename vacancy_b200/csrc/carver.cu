@@ -71,7 +71,13 @@ struct vcb_carver {
   size_t slot_floats = 0;
   Scratch max_sdf;       // one float per slot
   // 2D SDF scratch
-  Scratch mask_stage, sdf_scratch, absmax, sdf_views;
+  Scratch mask_stage, sdf_scratch, absmax;
+  // host masks are uploaded on a separate stream into a 2-deep ring of staging sets, so that the
+  // copy of one sub-batch overlaps the kernels of the previous ones
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+  bool consumed_valid[2] = {false, false};
+  unsigned stage_round = 0;
   size_t sdf_pix = 0;      // mask staging bytes per view
   size_t sdf_scr = 0;      // 2D-SDF scratch bytes per view
 
@@ -302,10 +308,11 @@ int ensure_sdf_scratch(vcb_carver* c, size_t pix, size_t scr) {
   pix = pix > c->sdf_pix ? pix : c->sdf_pix;
   scr = scr > c->sdf_scr ? scr : c->sdf_scr;
   pix = (pix + 255) & ~(size_t)255;
-  CU(c, c->mask_stage.reserve(pix * kSdfSubBatch));
+  if (c->copy_stream) CU(c, cudaStreamSynchronize(c->copy_stream));
+  CU(c, c->mask_stage.reserve(pix * kSdfSubBatch * 2));
   CU(c, c->sdf_scratch.reserve(scr * kSdfSubBatch));
   CU(c, c->absmax.reserve(sizeof(int) * kSdfSubBatch));
-  CU(c, c->sdf_views.reserve(sizeof(SdfView) * kSdfSubBatch));
+  c->consumed_valid[0] = c->consumed_valid[1] = false;
   c->sdf_pix = pix;
   c->sdf_scr = scr;
   return VCB_OK;
@@ -330,10 +337,22 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
   if ((rc = ensure_sdf_scratch(c, max_pix, max_scr)) != VCB_OK) return rc;
   float* pool = static_cast<float*>(c->pool.ptr);
   float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
+  if (!device_io && c->copy_stream == nullptr) {
+    CU(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (int s = 0; s < 2; s++) {
+      CU(c, cudaEventCreateWithFlags(&c->ev_copied[s], cudaEventDisableTiming));
+      CU(c, cudaEventCreateWithFlags(&c->ev_consumed[s], cudaEventDisableTiming));
+    }
+  }
   for (int first = 0; first < n_views;) {
     int nb = min(kSdfSubBatch, n_views - first);
     nb = min(nb, kMaxViewsPerLaunch - c->pending);
     SdfView hv[kSdfSubBatch];
+    const int set = (int)(c->stage_round & 1u);
+    if (!device_io && c->consumed_valid[set]) {
+      // the staging set may only be overwritten once the kernels that read it have finished
+      CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_consumed[set], 0));
+    }
     for (int i = 0; i < nb; i++) {
       const vcb_view& v = views[first + i];
       const size_t pix = (size_t)v.width * v.height;
@@ -341,8 +360,9 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
       if (device_io) {
         hv[i].mask = masks[first + i];
       } else {
-        uint8_t* dst = static_cast<uint8_t*>(c->mask_stage.ptr) + (size_t)i * c->sdf_pix;
-        CU(c, cudaMemcpyAsync(dst, masks[first + i], pix, cudaMemcpyHostToDevice, c->stream));
+        uint8_t* dst = static_cast<uint8_t*>(c->mask_stage.ptr) +
+                       (size_t)(set * kSdfSubBatch + i) * c->sdf_pix;
+        CU(c, cudaMemcpyAsync(dst, masks[first + i], pix, cudaMemcpyHostToDevice, c->copy_stream));
         hv[i].mask = dst;
       }
       hv[i].out = pool + (size_t)slot * c->slot_floats;
@@ -357,16 +377,21 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
       hv[i].ry1 = v.roi_max[1];
       fill_fuse_view(&c->fp.views[slot], v, hv[i].out, hv[i].max_out);
     }
-    // the descriptor array is small: pass it through a pageable async copy (staged by the driver)
-    CU(c, cudaMemcpyAsync(c->sdf_views.ptr, hv, sizeof(SdfView) * nb, cudaMemcpyHostToDevice,
-                          c->stream));
+    if (!device_io) {
+      CU(c, cudaEventRecord(c->ev_copied[set], c->copy_stream));
+      CU(c, cudaStreamWaitEvent(c->stream, c->ev_copied[set], 0));
+    }
     {
       Span span(c, 0);
-      launch_sdf2d(static_cast<SdfView*>(c->sdf_views.ptr), hv, nb, kSdfSigned,
-                   c->opt.sdf_minmax_normalize, c->opt.use_truncation, c->opt.truncation_band,
-                   c->stream, &c->stage_launches[0]);
+      launch_sdf2d(hv, nb, kSdfSigned, c->opt.sdf_minmax_normalize, c->opt.use_truncation,
+                   c->opt.truncation_band, c->stream, &c->stage_launches[0]);
     }
     CU(c, cudaGetLastError());
+    if (!device_io) {
+      CU(c, cudaEventRecord(c->ev_consumed[set], c->stream));
+      c->consumed_valid[set] = true;
+      c->stage_round++;
+    }
     if (sdf_out) {
       for (int i = 0; i < nb; i++) {
         if (!sdf_out[first + i]) continue;
@@ -383,8 +408,10 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
     }
   }
   if (!device_io) {
-    // host buffers are borrowed for the duration of the call only (voxel_carver.cc:394-413)
-    CU(c, cudaStreamSynchronize(c->stream));
+    // host buffers are borrowed for the duration of the call only (voxel_carver.cc:394-413): the
+    // masks have all been read once the copy stream is idle; the kernels may still be running
+    CU(c, cudaStreamSynchronize(c->copy_stream));
+    if (sdf_out) CU(c, cudaStreamSynchronize(c->stream));
   }
   return VCB_OK;
 }
@@ -511,14 +538,21 @@ void vcb_destroy(vcb_carver* c) {
   cudaSetDevice(c->opt.device);
   cudaStreamSynchronize(c->stream);
   resolve_spans(c);
+  if (c->copy_stream) {
+    cudaStreamSynchronize(c->copy_stream);
+    cudaStreamDestroy(c->copy_stream);
+    for (int s = 0; s < 2; s++) {
+      cudaEventDestroy(c->ev_copied[s]);
+      cudaEventDestroy(c->ev_consumed[s]);
+    }
+  }
   cudaFree(c->sdf_alloc);
   cudaFree(c->un);
   cudaFree(c->pos_x);
   cudaFree(c->pos_y);
   cudaFree(c->pos_z);
   cudaFree(c->wtab);
-  Scratch* all[] = {&c->pool, &c->max_sdf, &c->mask_stage, &c->sdf_scratch, &c->absmax,
-                    &c->sdf_views, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
+  Scratch* all[] = {&c->pool, &c->max_sdf, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
                     &c->iso.verts, &c->iso.faces, &c->iso.counters};
@@ -700,10 +734,8 @@ static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width,
   hv.rx1 = roi_max[0];
   hv.ry1 = roi_max[1];
   cudaError_t e = cudaMemcpy(base + off_mask, mask, pix, cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) e = cudaMemcpy(base + off_view, &hv, sizeof(hv), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) {
-    launch_sdf2d(reinterpret_cast<SdfView*>(base + off_view), &hv, 1, mode, normalize, truncate,
-                 band, nullptr, nullptr);
+    launch_sdf2d(&hv, 1, mode, normalize, truncate, band, nullptr, nullptr);
     e = cudaGetLastError();
   }
   if (e == cudaSuccess) e = cudaMemcpy(dist, base, pix * sizeof(float), cudaMemcpyDeviceToHost);

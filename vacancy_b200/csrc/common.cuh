@@ -67,8 +67,13 @@ enum SdfMode { kSdfSigned = 0, kSdfDistanceL1 = 1 };
 
 size_t sdf_scratch_bytes(int width, int height);  // per-view scratch of the 2D SDF kernels
 
-void launch_sdf2d(const SdfView* views_dev, const SdfView* views_host, int n_views, int mode,
-                  int normalize, int truncate, float band, cudaStream_t stream, int64_t* launches);
+// up to kSdfSubBatch view descriptors, passed to the kernels by value (kernel parameter bank)
+struct SdfBatch {
+  SdfView v[kSdfSubBatch];
+};
+
+void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normalize, int truncate,
+                  float band, cudaStream_t stream, int64_t* launches);
 void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_t stream,
                       int64_t* launches);
 void launch_fusion(FuseParams& p, int interp, int update, cudaStream_t stream,

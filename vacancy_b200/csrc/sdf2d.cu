@@ -68,8 +68,8 @@ __device__ __forceinline__ unsigned roi_word_mask(int x0, int rx0, int rx1) {
 
 // ---- pass 0: foreground bit-plane. One thread per 32-pixel word of a ROI row. -------------------
 // Only the value 255 is foreground (voxel_carver.cc:109).
-__global__ void __launch_bounds__(256) sdf_bits_kernel(const SdfView* __restrict__ views) {
-  const SdfView v = views[blockIdx.y];
+__global__ void __launch_bounds__(256) sdf_bits_kernel(const __grid_constant__ SdfBatch B) {
+  const SdfView& v = B.v[blockIdx.y];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     *v.absmax = 0;
     *v.max_out = -FLT_MAX;
@@ -105,8 +105,8 @@ __global__ void __launch_bounds__(256) sdf_bits_kernel(const SdfView* __restrict
 constexpr int kRowWarps = 8;
 constexpr int kMaxWordsPerRow = kMaxImageDim / 32;
 
-__global__ void __launch_bounds__(kRowWarps * 32) sdf_row_kernel(const SdfView* __restrict__ views) {
-  const SdfView v = views[blockIdx.y];
+__global__ void __launch_bounds__(kRowWarps * 32) sdf_row_kernel(const __grid_constant__ SdfBatch B) {
+  const SdfView& v = B.v[blockIdx.y];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int y = v.ry0 + blockIdx.x * kRowWarps + wib;
   if (y > v.ry1) return;
@@ -210,8 +210,8 @@ __global__ void __launch_bounds__(kRowWarps * 32) sdf_row_kernel(const SdfView* 
 constexpr int kColInf = 1 << 28;
 constexpr int kColSegs = 32;
 
-__global__ void __launch_bounds__(32 * kColSegs) sdf_col_kernel(const SdfView* __restrict__ views) {
-  const SdfView v = views[blockIdx.y];
+__global__ void __launch_bounds__(32 * kColSegs) sdf_col_kernel(const __grid_constant__ SdfBatch B) {
+  const SdfView& v = B.v[blockIdx.y];
   const int cx = threadIdx.x, seg = threadIdx.y;
   const int x = v.rx0 + blockIdx.x * 32 + cx;
   const bool col_ok = x <= v.rx1;
@@ -298,8 +298,8 @@ __global__ void __launch_bounds__(32 * kColSegs) sdf_col_kernel(const SdfView* _
 constexpr int kColMaxSegLen = 99;  // 32 cols * 32 segs * 99 rows * 2 B = 198 KB (+17 KB of carries)
 constexpr int kColFar = 1 << 20;
 
-__global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const SdfView* __restrict__ views) {
-  const SdfView v = views[blockIdx.y];
+__global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const __grid_constant__ SdfBatch B) {
+  const SdfView& v = B.v[blockIdx.y];
   const int cx = threadIdx.x, seg = threadIdx.y;
   const int x = v.rx0 + blockIdx.x * 32 + cx;
   if (v.rx0 + blockIdx.x * 32 > v.rx1) return;  // whole block outside this view's ROI
@@ -380,10 +380,10 @@ __global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const SdfView* __res
 }
 
 // ---- pass 3: int -> float, normalisation, truncation, image maximum. Block per group of rows. ---
-__global__ void __launch_bounds__(256) sdf_finalize_kernel(const SdfView* __restrict__ views,
+__global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant__ SdfBatch B,
                                                            int mode, int normalize, int truncate,
                                                            float band) {
-  const SdfView v = views[blockIdx.y];
+  const SdfView& v = B.v[blockIdx.y];
   float norm = 1.0f;
   bool do_norm = false;
   if (normalize && mode == kSdfSigned) {
@@ -445,12 +445,13 @@ __global__ void set_float_kernel(float* p, float v) { *p = v; }
 
 }  // namespace
 
-void launch_sdf2d(const SdfView* views_dev, const SdfView* views_host, int n_views, int mode,
-                  int normalize, int truncate, float band, cudaStream_t stream,
-                  int64_t* launches) {
+void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normalize, int truncate,
+                  float band, cudaStream_t stream, int64_t* launches) {
   int max_rows = 0, max_cols = 0, max_h = 0, max_words = 0;
+  SdfBatch views_dev;
   for (int i = 0; i < n_views; i++) {
     const SdfView& v = views_host[i];
+    views_dev.v[i] = v;
     max_rows = max(max_rows, v.ry1 - v.ry0 + 1);
     max_cols = max(max_cols, v.rx1 - v.rx0 + 1);
     max_h = max(max_h, v.height);
@@ -503,7 +504,7 @@ namespace vcb {
 namespace {
 
 constexpr int64_t kNoAllocMaxPixels = 2048LL * 2048LL;  // counted with the width rounded up to 32
-constexpr size_t kNoAllocHeader = 256;  // SdfView descriptor, abs-max and image-max cells
+constexpr size_t kNoAllocHeader = 256;  // abs-max and image-max cells
 // two int16 images + one bit per pixel + their 256-byte alignment slack
 constexpr size_t kNoAllocBytes =
     kNoAllocHeader + 2 * sizeof(int16_t) * kNoAllocMaxPixels + kNoAllocMaxPixels / 8 + 3 * 256;
@@ -514,10 +515,6 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
 // real address is asked for once per device (with that device current) and cached here.
 std::mutex g_noalloc_mutex;
 unsigned char* g_noalloc_ptr[64] = {nullptr};
-
-__global__ void sdf_noalloc_set_view_kernel(unsigned char* scratch, SdfView v) {
-  *reinterpret_cast<SdfView*>(scratch) = v;
-}
 
 }  // namespace
 }  // namespace vcb
@@ -579,9 +576,8 @@ extern "C" int vcb_make_signed_distance_field_noalloc(
   v.ry0 = roi_min[1];
   v.rx1 = roi_max[0];
   v.ry1 = roi_max[1];
-  sdf_noalloc_set_view_kernel<<<1, 1, 0, stream>>>(scratch, v);
-  launch_sdf2d(reinterpret_cast<const SdfView*>(scratch), &v, 1, kSdfSigned, minmax_normalize,
-               use_truncation, truncation_band, stream, nullptr);
+  launch_sdf2d(&v, 1, kSdfSigned, minmax_normalize, use_truncation, truncation_band, stream,
+               nullptr);
   e = cudaGetLastError();
   if (e != cudaSuccess) {
     snprintf(msg, sizeof(msg), "vcb_make_signed_distance_field_noalloc: %s", cudaGetErrorString(e));
