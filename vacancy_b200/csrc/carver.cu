@@ -555,7 +555,7 @@ void vcb_destroy(vcb_carver* c) {
   Scratch* all[] = {&c->pool, &c->max_sdf, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
-                    &c->iso.verts, &c->iso.faces, &c->iso.counters};
+                    &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo};
   for (Scratch* s : all) s->release();
   delete c;
 }

@@ -117,7 +117,7 @@ cudaError_t voxel_extract_flags(const GridDesc& g, VoxelExtract* st, uint8_t* fl
 
 struct IsoExtract {
   Scratch ibits, vbits, cbits, abits, segcnt, segbase, active, tmp, hkeys, hvals, verts, faces,
-      counters;
+      counters, cinfo;
   int64_t n_vertices = -1, n_faces = -1;
   int phase = 0;          // 0 nothing, 1 counted, 2 vertices emitted, 3 faces emitted
   unsigned n_active = 0;  // active segments

@@ -83,7 +83,11 @@ __device__ __forceinline__ unsigned get_bit(const uint32_t* __restrict__ bits, c
 }
 
 // ---- dense pass ---------------------------------------------------------------------------------
-constexpr int kBitsRows = 4;  // rows per block iteration: 4 independent loads in flight per thread
+// One block per kBitsRows grid rows; a warp iteration covers 128 voxels of each row with four
+// coalesced 128-byte loads per row (16 independent loads in flight per thread), turns every 32
+// voxels into one word of each bitmap with a ballot, and lanes 0-3 store the four words together.
+// ~0.25 instructions per voxel: the pass is bound by HBM, not by issue.
+constexpr int kBitsRows = 4;
 
 __global__ void __launch_bounds__(256) mc_bits_kernel(const float* __restrict__ sdf_stored,
                                                       int nx, int spr, int64_t n_rows, float thr,
@@ -92,23 +96,38 @@ __global__ void __launch_bounds__(256) mc_bits_kernel(const float* __restrict__ 
   const int lane = threadIdx.x & 31;
   const int warps = blockDim.x >> 5;
   const int64_t row0 = (int64_t)blockIdx.x * kBitsRows;
-  for (int sx = threadIdx.x >> 5; sx < spr; sx += warps) {
-    const int x = sx * 32 + lane;
-    float s[kBitsRows];
+  const int rows = (int)min((int64_t)kBitsRows, n_rows - row0);
+  const float* __restrict__ src = sdf_stored + row0 * nx;
+  uint32_t* __restrict__ idst = ibits + row0 * spr;
+  uint32_t* __restrict__ vdst = vbits + row0 * spr;
+  const int groups = (spr + 3) / 4;
+  for (int c = threadIdx.x >> 5; c < groups; c += warps) {
+    const int x = c * 128 + lane;
+    float s[kBitsRows][4];
 #pragma unroll
     for (int r = 0; r < kBitsRows; r++) {
-      const int64_t row = row0 + r;
-      s[r] = (x < nx && row < n_rows) ? sdf_stored[row * nx + x] : kInvalidSdf;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        s[r][q] = (r < rows && x + 32 * q < nx) ? __ldg(src + r * nx + x + 32 * q) : kInvalidSdf;
+      }
     }
 #pragma unroll
     for (int r = 0; r < kBitsRows; r++) {
-      const int64_t row = row0 + r;
-      const bool valid = (x < nx) && (s[r] != kInvalidSdf);
-      const unsigned iw = __ballot_sync(0xffffffffu, valid && (s[r] < thr));
-      const unsigned vw = __ballot_sync(0xffffffffu, valid);
-      if (lane == 0 && row < n_rows) {
-        ibits[row * spr + sx] = iw;
-        vbits[row * spr + sx] = vw;
+      unsigned iw = 0, vw = 0;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const bool valid = s[r][q] != kInvalidSdf;  // positions beyond nx hold kVal
+        const unsigned i_q = __ballot_sync(0xffffffffu, valid && (s[r][q] < thr));
+        const unsigned v_q = __ballot_sync(0xffffffffu, valid);
+        if (lane == q) {
+          iw = i_q;
+          vw = v_q;
+        }
+      }
+      const int w = c * 4 + lane;
+      if (lane < 4 && r < rows && w < spr) {
+        idst[r * spr + w] = iw;
+        vdst[r * spr + w] = vw;
       }
     }
   }
@@ -138,8 +157,7 @@ __global__ void __launch_bounds__(256)
     mc_cube_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
                    const uint32_t* __restrict__ vbits, const uint32_t* __restrict__ ubits,
                    uint32_t* __restrict__ cbits, uint32_t* __restrict__ abits,
-                   uint64_t* __restrict__ segcnt, uint32_t* __restrict__ active,
-                   unsigned* __restrict__ n_active) {
+                   uint32_t* __restrict__ active, unsigned* __restrict__ n_active) {
   const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= m.n_words) return;
   const int sx = (int)(w % m.spr);
@@ -166,7 +184,6 @@ __global__ void __launch_bounds__(256)
   if (z >= m.z_begin) {
     const int64_t seg = seg_index(m, sx, y, z);
     abits[seg] = a;
-    segcnt[seg] = 0;
     if (a) active[atomicAdd(n_active, 1u)] = (uint32_t)seg;
   }
 }
@@ -264,26 +281,55 @@ __device__ __forceinline__ void seg_coords(const McGeom& m, int64_t seg, int* sx
   *z = (int)(row / m.ny) + m.z_begin;
 }
 
+// (vertex, face) numbers of a segment's first cube: the row's exclusive prefix (scan over rows) plus
+// the counts of the segments before it in the same row, summed by the warp.
+__device__ __forceinline__ void seg_base(const McGeom& m, int64_t seg, int lane,
+                                         const uint32_t* __restrict__ segcnt,
+                                         const uint64_t* __restrict__ rowbase, int64_t* vbase,
+                                         int64_t* fbase) {
+  const int64_t row = seg / m.spr;
+  const int sx = (int)(seg - row * m.spr);
+  unsigned nv = 0, nt = 0;
+  for (int s0 = 0; s0 < sx; s0 += 32) {
+    const int sidx = s0 + lane;
+    const unsigned c = sidx < sx ? segcnt[row * m.spr + sidx] : 0u;
+    nv += c >> 16;
+    nt += c & 0xffffu;
+  }
+  nv = __reduce_add_sync(0xffffffffu, nv);
+  nt = __reduce_add_sync(0xffffffffu, nt);
+  const uint64_t rb = rowbase[row];
+  *vbase = (int64_t)(rb >> 32) + nv;
+  *fbase = (int64_t)(rb & 0xffffffffull) + nt;
+}
+
 __global__ void __launch_bounds__(128)
     mc_count_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
                     const uint32_t* __restrict__ cbits, const uint32_t* __restrict__ abits,
                     const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
-                    uint64_t* __restrict__ segcnt) {
+                    uint32_t* __restrict__ segcnt, unsigned long long* __restrict__ rowcnt,
+                    uint32_t* __restrict__ cinfo) {
   const int lane = threadIdx.x & 31;
   const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (wid >= *n_active) return;
   const int64_t seg = active[wid];
   int sx, y, z;
   seg_coords(m, seg, &sx, &y, &z);
-  unsigned nv = 0, nt = 0;
+  unsigned nv = 0, nt = 0, packed = 0;
   if ((abits[seg] >> lane) & 1u) {
     const CubeInfo info = cube_info(m, ibits, cbits, sx * 32 + lane, y, z);
     nv = __popc(info.owned);
     nt = d_ntri[info.ci];
+    packed = (unsigned)info.ci | (info.owned << 8) | 0x80000000u;
   }
+  cinfo[(size_t)wid * 32 + lane] = packed;  // cube index + owned-edge mask, reused by the emit passes
   nv = __reduce_add_sync(0xffffffffu, nv);
   nt = __reduce_add_sync(0xffffffffu, nt);
-  if (lane == 0) segcnt[seg] = ((uint64_t)nv << 32) | nt;
+  if (lane == 0) {
+    // per segment: (vertices << 16) | faces (<= 384 and <= 160); per row of segments: 64-bit sums
+    segcnt[seg] = (nv << 16) | nt;
+    atomicAdd(rowcnt + seg / m.spr, ((unsigned long long)nv << 32) | nt);
+  }
 }
 
 // marching_cubes.cc:25-47, float64, one rounding per operation
@@ -313,7 +359,8 @@ __global__ void __launch_bounds__(128)
     mc_vertex_kernel(const McGeom m, const GridDesc g, const uint32_t* __restrict__ ibits,
                      const uint32_t* __restrict__ cbits, const uint32_t* __restrict__ abits,
                      const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
-                     const uint64_t* __restrict__ segbase, double iso, int linear_interp,
+                     const uint32_t* __restrict__ segcnt, const uint64_t* __restrict__ rowbase,
+                     const uint32_t* __restrict__ cinfo, double iso, int linear_interp,
                      int64_t vertex_offset, float* __restrict__ vertices, uint64_t* hkeys,
                      int32_t* hvals, uint64_t hmask) {
   const int lane = threadIdx.x & 31;
@@ -323,19 +370,20 @@ __global__ void __launch_bounds__(128)
   int sx, y, z;
   seg_coords(m, seg, &sx, &y, &z);
   const int x = sx * 32 + lane;
-  const bool act = (abits[seg] >> lane) & 1u;
+  const unsigned packed = cinfo[(size_t)wid * 32 + lane];
   CubeInfo info;
-  info.ci = 0;
-  info.owned = 0;
-  if (act) info = cube_info(m, ibits, cbits, x, y, z);
+  info.ci = (int)(packed & 0xffu);
+  info.owned = (packed >> 8) & 0xfffu;
   const unsigned nv = __popc(info.owned);
   unsigned inc = nv;
   for (int o = 1; o < 32; o <<= 1) {
     const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
     if (lane >= o) inc += t;
   }
+  int64_t vbase, fbase;
+  seg_base(m, seg, lane, segcnt, rowbase, &vbase, &fbase);
   if (nv == 0) return;
-  int64_t vid = (int64_t)(segbase[seg] >> 32) + (inc - nv);
+  int64_t vid = vbase + (inc - nv);
   // corner values and positions
   const size_t plane = (size_t)m.nx * m.ny;
   float val[8], pos[8][3];
@@ -375,7 +423,8 @@ __global__ void __launch_bounds__(128)
 __global__ void __launch_bounds__(128)
     mc_face_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
                    const uint32_t* __restrict__ abits, const uint32_t* __restrict__ active,
-                   const unsigned* __restrict__ n_active, const uint64_t* __restrict__ segbase,
+                   const unsigned* __restrict__ n_active, const uint32_t* __restrict__ segcnt,
+                   const uint64_t* __restrict__ rowbase, const uint32_t* __restrict__ cinfo,
                    int32_t* __restrict__ faces, const uint64_t* __restrict__ hkeys,
                    const int32_t* __restrict__ hvals, uint64_t hmask) {
   const int lane = threadIdx.x & 31;
@@ -385,28 +434,33 @@ __global__ void __launch_bounds__(128)
   int sx, y, z;
   seg_coords(m, seg, &sx, &y, &z);
   const int x = sx * 32 + lane;
-  const bool act = (abits[seg] >> lane) & 1u;
-  int ci = 0;
-  if (act) {
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      ci |= (int)get_bit(ibits, m, x + c_corner[k][0], y + c_corner[k][1], z + c_corner[k][2]) << k;
-    }
-  }
+  const unsigned packed = cinfo[(size_t)wid * 32 + lane];
+  const bool act = packed != 0;
+  const int ci = (int)(packed & 0xffu);
   const unsigned nt = act ? d_ntri[ci] : 0;
   unsigned inc = nt;
   for (int o = 1; o < 32; o <<= 1) {
     const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
     if (lane >= o) inc += t;
   }
+  int64_t vbase, fbase;
+  seg_base(m, seg, lane, segcnt, rowbase, &vbase, &fbase);
   if (nt == 0) return;
-  int64_t fid = (int64_t)(segbase[seg] & 0xffffffffull) + (inc - nt);
+  int64_t fid = fbase + (inc - nt);
+  // each crossed edge is looked up once, however many triangles share it
+  int32_t vid[12];
+  unsigned em = d_edge_mask[ci];
+  while (em) {
+    const int e = __ffs(em) - 1;
+    em &= em - 1;
+    vid[e] = hash_find(hkeys, hvals, hmask, edge_key(m, x, y, z, e));
+  }
   const uint64_t tri = d_tri[ci];
   for (unsigned t = 0; t < nt; t++) {
 #pragma unroll
     for (int j = 0; j < 3; j++) {  // face[j] = vertex of edge tri[i + (2 - j)], :202-204
       const int e = (int)((tri >> (4 * (3 * t + 2 - j))) & 0xF);
-      faces[fid * 3 + j] = hash_find(hkeys, hvals, hmask, edge_key(m, x, y, z, e));
+      faces[fid * 3 + j] = vid[e];
     }
     fid++;
   }
@@ -494,16 +548,19 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
   VCB_TRY(st->vbits.reserve(wbytes));
   VCB_TRY(st->cbits.reserve(wbytes));
   VCB_TRY(st->abits.reserve((size_t)m.n_segs * sizeof(uint32_t)));
-  VCB_TRY(st->segcnt.reserve((size_t)(m.n_segs + 1) * sizeof(uint64_t)));
-  VCB_TRY(st->segbase.reserve((size_t)(m.n_segs + 1) * sizeof(uint64_t)));
+  const int64_t n_rows_owned = (int64_t)g.ny * (g.z_end - g.z_begin);
+  VCB_TRY(st->segcnt.reserve((size_t)m.n_segs * sizeof(uint32_t)));
+  // per row of segments: [0, n_rows) counts, then [n_rows + 1 .. ) exclusive prefix + total
+  VCB_TRY(st->segbase.reserve((size_t)(2 * n_rows_owned + 2) * sizeof(uint64_t)));
   VCB_TRY(st->active.reserve((size_t)m.n_segs * sizeof(uint32_t)));
   VCB_TRY(st->counters.reserve(256));
   uint32_t* ibits = static_cast<uint32_t*>(st->ibits.ptr);
   uint32_t* vbits = static_cast<uint32_t*>(st->vbits.ptr);
   uint32_t* cbits = static_cast<uint32_t*>(st->cbits.ptr);
   uint32_t* abits = static_cast<uint32_t*>(st->abits.ptr);
-  uint64_t* segcnt = static_cast<uint64_t*>(st->segcnt.ptr);
-  uint64_t* segbase = static_cast<uint64_t*>(st->segbase.ptr);
+  uint32_t* segcnt = static_cast<uint32_t*>(st->segcnt.ptr);
+  uint64_t* rowcnt = static_cast<uint64_t*>(st->segbase.ptr);
+  uint64_t* rowbase = rowcnt + n_rows_owned;
   uint32_t* active = static_cast<uint32_t*>(st->active.ptr);
   unsigned* n_active = static_cast<unsigned*>(st->counters.ptr);
   uint32_t* ubits = nullptr;
@@ -523,7 +580,9 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
     if (launches) *launches += 1;
   }
   mc_cube_kernel<<<(unsigned)((m.n_words + 255) / 256), 256, 0, stream>>>(
-      m, ibits, vbits, ubits, cbits, abits, segcnt, active, n_active);
+      m, ibits, vbits, ubits, cbits, abits, active, n_active);
+  VCB_TRY(cudaMemsetAsync(segcnt, 0, (size_t)m.n_segs * sizeof(uint32_t), stream));
+  VCB_TRY(cudaMemsetAsync(rowcnt, 0, (size_t)n_rows_owned * sizeof(uint64_t), stream));
   if (launches) *launches += 1;
   unsigned h_active = 0;
   VCB_TRY(cudaMemcpyAsync(&h_active, n_active, sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
@@ -531,14 +590,17 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
   st->n_active = h_active;
   const unsigned wblocks = (h_active + 3) / 4;  // 4 warps per block
   if (h_active > 0) {
-    mc_count_kernel<<<wblocks, 128, 0, stream>>>(m, ibits, cbits, abits, active, n_active, segcnt);
+    VCB_TRY(st->cinfo.reserve((size_t)h_active * 32 * sizeof(uint32_t)));
+    mc_count_kernel<<<wblocks, 128, 0, stream>>>(
+        m, ibits, cbits, abits, active, n_active, segcnt,
+        reinterpret_cast<unsigned long long*>(rowcnt), static_cast<uint32_t*>(st->cinfo.ptr));
     if (launches) *launches += 1;
   }
   // the ubits scratch (st->tmp) is dead from here on; the scan reuses st->tmp
-  VCB_TRY(scan_exclusive_u64(segcnt, segbase, m.n_segs, segbase + m.n_segs, &st->tmp, stream,
-                             launches));
+  VCB_TRY(scan_exclusive_u64(rowcnt, rowbase, n_rows_owned, rowbase + n_rows_owned, &st->tmp,
+                             stream, launches));
   uint64_t total = 0;
-  VCB_TRY(cudaMemcpyAsync(&total, segbase + m.n_segs, sizeof(total), cudaMemcpyDeviceToHost,
+  VCB_TRY(cudaMemcpyAsync(&total, rowbase + n_rows_owned, sizeof(total), cudaMemcpyDeviceToHost,
                           stream));
   VCB_TRY(cudaStreamSynchronize(stream));
   st->n_vertices = (int64_t)(total >> 32);
@@ -569,8 +631,9 @@ cudaError_t iso_emit_vertices(const GridDesc& g, int64_t vertex_offset, IsoExtra
     mc_vertex_kernel<<<(st->n_active + 3) / 4, 128, 0, stream>>>(
         m, g, static_cast<uint32_t*>(st->ibits.ptr), static_cast<uint32_t*>(st->cbits.ptr),
         static_cast<uint32_t*>(st->abits.ptr), static_cast<uint32_t*>(st->active.ptr),
-        static_cast<unsigned*>(st->counters.ptr), static_cast<uint64_t*>(st->segbase.ptr),
-        st->iso_level, st->linear_interp, vertex_offset, static_cast<float*>(st->verts.ptr),
+        static_cast<unsigned*>(st->counters.ptr), static_cast<uint32_t*>(st->segcnt.ptr),
+        static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin),
+        static_cast<uint32_t*>(st->cinfo.ptr), st->iso_level, st->linear_interp, vertex_offset, static_cast<float*>(st->verts.ptr),
         static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), st->hmask);
     if (launches) *launches += 1;
   }
@@ -609,7 +672,9 @@ cudaError_t iso_emit_faces(const GridDesc& g, IsoExtract* st, cudaStream_t strea
     mc_face_kernel<<<(st->n_active + 3) / 4, 128, 0, stream>>>(
         m, static_cast<uint32_t*>(st->ibits.ptr), static_cast<uint32_t*>(st->abits.ptr),
         static_cast<uint32_t*>(st->active.ptr), static_cast<unsigned*>(st->counters.ptr),
-        static_cast<uint64_t*>(st->segbase.ptr), static_cast<int32_t*>(st->faces.ptr),
+        static_cast<uint32_t*>(st->segcnt.ptr),
+        static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin),
+        static_cast<uint32_t*>(st->cinfo.ptr), static_cast<int32_t*>(st->faces.ptr),
         static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), st->hmask);
     if (launches) *launches += 1;
   }
