@@ -269,6 +269,14 @@ def run_ours(args, cfg):
     fus_ms_per_launch = fus_ms / max(fus_launches, 1)
     achieved = bytes_per_launch / (fus_ms_per_launch * 1e-3) / 1e9
     launches_per_step = sum(v[1] for v in stages.values()) / args.steps
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "fuse_kernel_traffic.json")
+    if world == 1 and os.path.exists(tpath):
+        with open(tpath) as f:
+            t = json.load(f).get(cfg["name"])
+        if t:  # ncu capture of a full 64-view launch; scale to this run's average views per launch
+            traffic = (t["dram_bytes_read"] + t["dram_bytes_write"]) * views_per_launch / \
+                t["views_in_launch"]
 
     line = {
         "metric": "carve_gvoxel_view_updates_per_s", "value": updates / (ms_step * 1e-3) / 1e9,
@@ -288,14 +296,22 @@ def run_ours(args, cfg):
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "roofline": {"kernel": "fuse_kernel", "bound": "hbm", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                     "traffic": None, "peak_source": peak_src,
+                     "traffic": traffic, "peak_source": peak_src,
+                     "traffic_source": "ncu --set full capture of a 64-view launch, scaled to the "
+                                       "average views per launch (profiles/fuse_kernel_traffic.json)"
+                                       if traffic else None,
                      "bytes_per_launch": bytes_per_launch, "ms_per_launch": fus_ms_per_launch,
                      "note": "batched fusion is FP32/ALU-issue bound, not HBM bound (SURVEY.md 8d); "
                              "see fp32"},
         "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items()},
         "mc": {"ms": stages["marching_cubes"][0] / args.steps,
                "gvoxel_per_s": nvox / world / (stages["marching_cubes"][0] / args.steps * 1e-3) / 1e9,
-               "vertices": int(counts[0]), "faces": int(counts[1])},
+               "vertices": int(counts[0]), "faces": int(counts[1]),
+               # algorithmic bytes: 4 B per voxel + 12 B per vertex + 12 B per face
+               "algorithmic_gbs": (4.0 * nvox + 12.0 * (counts[0] + counts[1])) / world /
+               (stages["marching_cubes"][0] / args.steps * 1e-3) / 1e9,
+               "frac_of_hbm_peak": (4.0 * nvox + 12.0 * (counts[0] + counts[1])) / world /
+               (stages["marching_cubes"][0] / args.steps * 1e-3) / 1e9 / hbm_peak},
         "fusion_gvv_per_s": updates / world / (fus_ms / args.steps * 1e-3) / 1e9,
     }
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
