@@ -70,6 +70,9 @@ struct vcb_carver {
   Scratch pool;          // kMaxViewsPerLaunch image slots
   size_t slot_floats = 0;
   Scratch max_sdf;       // one float per slot
+  Scratch tiles;         // 8x8-block flags per slot (tile_flag_bytes), see fusion.cu
+  size_t tile_slot_bytes = 0;
+  bool use_tiles = true;
   // 2D SDF scratch
   Scratch mask_stage, sdf_scratch, absmax;
   // host masks are uploaded on a separate stream into a 2-deep ring of staging sets, so that the
@@ -91,6 +94,8 @@ struct vcb_carver {
 };
 
 namespace {
+
+int flush_pending(vcb_carver* c);
 
 int fail(vcb_carver* c, int code, const char* fmt, ...) {
   char buf[512];
@@ -212,6 +217,41 @@ void fill_fuse_view(FuseView* f, const vcb_view& v, const float* image, const fl
   f->model = v.model;
   f->image = image;
   f->max_sdf = max_sdf;
+  f->tiles = nullptr;
+  f->tile_words = f->tile_rows = 0;
+}
+
+// flag storage for every slot of the view queue, sized for the largest image seen so far
+int ensure_tiles(vcb_carver* c, int width, int height) {
+  const size_t need = (tile_flag_bytes(width, height) + 255) & ~(size_t)255;
+  if (need <= c->tile_slot_bytes && c->tiles.ptr) return VCB_OK;
+  int rc = flush_pending(c);
+  if (rc != VCB_OK) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  CU(c, c->tiles.reserve(need * kMaxViewsPerLaunch));
+  c->tile_slot_bytes = need;
+  return VCB_OK;
+}
+
+// queues the block-flag kernel for `n` freshly written images and points their views at the flags
+void attach_tiles(vcb_carver* c, const int* slots, const float* const* images, const vcb_view* views,
+                  int n) {
+  if (!c->use_tiles || c->opt.sdf_interp != VCB_INTERP_BILINEAR) return;
+  TileBatch b;
+  for (int i = 0; i < n; i++) {
+    uint32_t* flags = reinterpret_cast<uint32_t*>(static_cast<unsigned char*>(c->tiles.ptr) +
+                                                  (size_t)slots[i] * c->tile_slot_bytes);
+    b.image[i] = images[i];
+    b.flags[i] = flags;
+    b.width[i] = views[i].width;
+    b.height[i] = views[i].height;
+    FuseView& f = c->fp.views[slots[i]];
+    f.tiles = flags;
+    f.tile_words = tile_words_for(views[i].width);
+    f.tile_rows = tile_rows_for(views[i].height);
+  }
+  Span span(c, 0);
+  launch_tile_flags(b, n, c->stream, &c->stage_launches[0]);
 }
 
 GridDesc grid_desc(const vcb_carver* c) {
@@ -335,6 +375,14 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
   if (n_views == 0) return VCB_OK;
   if ((rc = ensure_pool(c, max_pix)) != VCB_OK) return rc;
   if ((rc = ensure_sdf_scratch(c, max_pix, max_scr)) != VCB_OK) return rc;
+  {
+    int mw = 0, mh = 0;
+    for (int i = 0; i < n_views; i++) {
+      mw = max(mw, views[i].width);
+      mh = max(mh, views[i].height);
+    }
+    if ((rc = ensure_tiles(c, mw, mh)) != VCB_OK) return rc;
+  }
   float* pool = static_cast<float*>(c->pool.ptr);
   float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
   if (!device_io && c->copy_stream == nullptr) {
@@ -387,6 +435,16 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
                    c->opt.truncation_band, c->stream, &c->stage_launches[0]);
     }
     CU(c, cudaGetLastError());
+    {
+      int slots[kSdfSubBatch];
+      const float* imgs[kSdfSubBatch];
+      for (int i = 0; i < nb; i++) {
+        slots[i] = c->pending + i;
+        imgs[i] = hv[i].out;
+      }
+      attach_tiles(c, slots, imgs, views + first, nb);
+      CU(c, cudaGetLastError());
+    }
     if (!device_io) {
       CU(c, cudaEventRecord(c->ev_consumed[set], c->stream));
       c->consumed_valid[set] = true;
@@ -467,6 +525,10 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
   c->z_begin = z0;
   c->z_end = z1;
   c->halo = z0 < 2 ? z0 : 2;
+  {
+    const char* e = getenv("VACANCY_B200_NO_TILES");  // debugging switch: no tile classification
+    c->use_tiles = !(e && e[0] == '1');
+  }
 #define CREATE_TRY(call)                                                                     \
   do {                                                                                       \
     cudaError_t e_ = (call);                                                                 \
@@ -552,7 +614,7 @@ void vcb_destroy(vcb_carver* c) {
   cudaFree(c->pos_y);
   cudaFree(c->pos_z);
   cudaFree(c->wtab);
-  Scratch* all[] = {&c->pool, &c->max_sdf, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
+  Scratch* all[] = {&c->pool, &c->max_sdf, &c->tiles, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
                     &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo};
@@ -646,6 +708,14 @@ int vcb_carve_sdfs(vcb_carver* c, int32_t n_views, const vcb_view* views,
   }
   if (n_views == 0) return VCB_OK;
   if ((rc = ensure_pool(c, max_pix)) != VCB_OK) return rc;
+  {
+    int mw = 0, mh = 0;
+    for (int i = 0; i < n_views; i++) {
+      mw = max(mw, views[i].width);
+      mh = max(mh, views[i].height);
+    }
+    if ((rc = ensure_tiles(c, mw, mh)) != VCB_OK) return rc;
+  }
   float* pool = static_cast<float*>(c->pool.ptr);
   float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
   for (int i = 0; i < n_views; i++) {
@@ -659,6 +729,10 @@ int vcb_carve_sdfs(vcb_carver* c, int32_t n_views, const vcb_view* views,
       launch_image_max(dst, (int64_t)pix, max_sdf + slot, c->stream, &c->stage_launches[0]);
     }
     fill_fuse_view(&c->fp.views[slot], v, dst, max_sdf + slot);
+    {
+      const float* img = dst;
+      attach_tiles(c, &slot, &img, &v, 1);
+    }
     c->pending++;
     if (c->pending == kMaxViewsPerLaunch) {
       if ((rc = flush_pending(c)) != VCB_OK) return rc;
@@ -679,6 +753,14 @@ int vcb_carve_sdfs_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
     if (!sdfs_dev[i]) return fail(c, VCB_ERR_INVALID, "sdf %d is null", i);
   }
   if ((rc = flush_pending(c)) != VCB_OK) return rc;
+  {
+    int mw = 0, mh = 0;
+    for (int i = 0; i < n_views; i++) {
+      mw = max(mw, views[i].width);
+      mh = max(mh, views[i].height);
+    }
+    if (n_views > 0 && (rc = ensure_tiles(c, mw, mh)) != VCB_OK) return rc;
+  }
   float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
   for (int i = 0; i < n_views; i++) {
     const vcb_view& v = views[i];
@@ -689,6 +771,7 @@ int vcb_carve_sdfs_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
                        &c->stage_launches[0]);
     }
     fill_fuse_view(&c->fp.views[slot], v, sdfs_dev[i], max_sdf + slot);
+    attach_tiles(c, &slot, &sdfs_dev[i], &v, 1);
     c->pending++;
     if (c->pending == kMaxViewsPerLaunch || i == n_views - 1) {
       if ((rc = flush_pending(c)) != VCB_OK) return rc;

@@ -32,7 +32,24 @@ struct FuseView {
   int fast;            // set by launch_fusion: pinhole with intrinsics in the shared-reciprocal range
   const float* image;  // device SDF image
   const float* max_sdf;  // device scalar: max over the whole image (only read for VCB_OUTSIDE_MAX)
+  // 8x8-pixel block flags of the image, one bit per block, tile_rows x tile_words words each:
+  // [all 64 texels == 1.0f] followed by [all 64 texels == kVal]; NULL = no flags
+  const uint32_t* tiles;
+  int tile_words, tile_rows;
 };
+
+constexpr int kTilePx = 8;  // edge of a flagged pixel block
+inline int tile_words_for(int width) { return ((width + kTilePx - 1) / kTilePx + 31) / 32; }
+inline int tile_rows_for(int height) { return (height + kTilePx - 1) / kTilePx; }
+inline size_t tile_flag_bytes(int width, int height) {
+  return (size_t)2 * tile_words_for(width) * tile_rows_for(height) * sizeof(uint32_t);
+}
+struct TileBatch {
+  const float* image[kSdfSubBatch];
+  uint32_t* flags[kSdfSubBatch];
+  int width[kSdfSubBatch], height[kSdfSubBatch];
+};
+void launch_tile_flags(const TileBatch& b, int n, cudaStream_t stream, int64_t* launches);
 
 struct FuseParams {
   float* sdf;            // slab state, plane z_begin first
