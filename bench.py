@@ -243,6 +243,14 @@ def run_ours(args, cfg):
 
     for _ in range(args.warmup):
         step_resident()
+    if world > 1 and not args.no_rebalance:
+        # the slabs do not cost the same (edge slabs see the cameras differently): re-partition once
+        # from the measured fusion time of the warm-up passes, then warm up again
+        ranges = car.rebalance(car.stage_times()["fusion"][0])
+        for _ in range(args.warmup):
+            step_resident()
+    else:
+        ranges = car.ranges
     car.stage_times()  # clear the per-stage counters
     sampler = ClockSampler(local)
     if rank == 0:
@@ -251,6 +259,15 @@ def run_ours(args, cfg):
     clocks = sampler.stop() if rank == 0 else None
     stages = car.stage_times()
     ms_step = ms_total / args.steps
+    per_rank = None
+    if world > 1:  # how evenly the slabs split the work (rank order = slab order, bottom to top)
+        mine = torch.tensor([stages["fusion"][0] / args.steps, stages["sdf2d"][0] / args.steps,
+                             stages["marching_cubes"][0] / args.steps], device="cuda")
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"fusion_ms": [round(float(t[0]), 2) for t in allr],
+                    "sdf2d_ms": [round(float(t[1]), 2) for t in allr],
+                    "marching_cubes_ms": [round(float(t[2]), 2) for t in allr]}
 
     for _ in range(min(args.warmup, 2)):
         step_e2e()
@@ -285,6 +302,7 @@ def run_ours(args, cfg):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": describe(cfg), "grid": [n, n, n], "views": V, "image": [size, size],
                    "parallelism": "z-slab x%d" % world,
+                   "slabs": [list(r) for r in ranges],
                    "l2": "inputs larger than L2 (masks %.2f GB, grid state %.2f GB per step)"
                          % (V * size * size / 1e9, 8 * nvox / 1e9),
                    "step": "reset + 2D SDF of every view + fusion (64 views/launch) + marching cubes"},
@@ -313,6 +331,7 @@ def run_ours(args, cfg):
                "frac_of_hbm_peak": (4.0 * nvox + 12.0 * (counts[0] + counts[1])) / world /
                (stages["marching_cubes"][0] / args.steps * 1e-3) / 1e9 / hbm_peak},
         "fusion_gvv_per_s": updates / world / (fus_ms / args.steps * 1e-3) / 1e9,
+        "per_rank": per_rank,
     }
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
     ops = 54.0 if cfg["weighted"] else 48.0  # reference-order FP32 ops per voxel-view, SURVEY.md 8d
@@ -345,6 +364,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg4", choices=sorted(S.CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-rebalance", action="store_true",
+                    help="keep the equal-thickness z slabs (multi-GPU)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     cfg = workload(args.workload)

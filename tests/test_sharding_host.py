@@ -23,6 +23,21 @@ def test_slab_ranges_cover_grid():
         sharded.slab_ranges(7, 4)
 
 
+def test_rebalanced_ranges():
+    ranges = sharded.slab_ranges(1024, 8)
+    # equal costs: nothing moves
+    assert sharded.rebalanced_ranges(ranges, [1.0] * 8) == ranges
+    # heavier edge slabs get thinner, the partition stays contiguous and complete
+    new = sharded.rebalanced_ranges(ranges, [118.8, 105.8, 102.5, 102.5, 101.9, 102.9, 106.5, 118.5])
+    assert new[0][0] == 0 and new[-1][1] == 1024
+    assert all(a[1] == b[0] for a, b in zip(new[:-1], new[1:]))
+    sizes = [b - a for a, b in new]
+    assert sizes[0] < 128 and sizes[-1] < 128 and max(sizes) > 128 and min(sizes) >= 2
+    # degenerate costs still leave every slab its two halo planes
+    tiny = sharded.rebalanced_ranges(sharded.slab_ranges(8, 4), [100.0, 0.0, 0.0, 0.0])
+    assert all(b - a >= 2 for a, b in tiny) and tiny[-1][1] == 8
+
+
 def test_exclusive_offsets():
     off, total = sharded.exclusive_offsets([(5, 9), (0, 0), (7, 2)])
     assert off.tolist() == [[0, 0], [5, 9], [5, 9]] and total.tolist() == [12, 11]

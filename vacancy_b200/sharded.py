@@ -38,6 +38,27 @@ def slab_ranges(nz, world):
     return out
 
 
+def rebalanced_ranges(ranges, cost, min_planes=2):
+    """New contiguous z ranges with (approximately) equal cost, given the measured cost of each
+    current slab (e.g. its fusion time); the cost per plane is taken as constant inside a slab.
+    Deterministic, so every rank computes the same partition from the gathered costs."""
+    world = len(ranges)
+    nz = ranges[-1][1]
+    density = np.empty(nz, np.float64)
+    for (a, b), c in zip(ranges, cost):
+        density[a:b] = max(float(c), 1e-9) / (b - a)
+    cum = np.concatenate([[0.0], np.cumsum(density)])
+    bounds = [0]
+    for r in range(1, world):
+        target = cum[-1] * r / world
+        z = int(np.searchsorted(cum, target))
+        z = max(z, bounds[-1] + min_planes)
+        z = min(z, nz - min_planes * (world - r))
+        bounds.append(z)
+    bounds.append(nz)
+    return [(bounds[i], bounds[i + 1]) for i in range(world)]
+
+
 def exclusive_offsets(counts):
     """counts[r] = (vertices, faces) of slab r -> per-slab (vertex_offset, face_offset), totals."""
     counts = np.asarray(counts, np.int64).reshape(-1, 2)
@@ -183,13 +204,38 @@ class ShardedCarver:
         # number of z planes as VoxelGrid::Init computes it (float32, voxel_carver.cc:294-296)
         nz = int((np.float32(option.bb_max[2]) - np.float32(option.bb_min[2])) /
                  np.float32(option.resolution))
-        self.z_range = slab_ranges(nz, world)[rank] if world > 1 else None
+        self.option, self.device_index = option, device
+        self.ranges = slab_ranges(nz, world) if world > 1 else [(0, nz)]
         self.stream = stream if stream is not None else torch.cuda.current_stream()
-        self.slab = _Slab(option, self.z_range, device, self.stream)
+        self._build()
+
+    def _build(self):
+        self.z_range = self.ranges[self.rank] if self.world > 1 else None
+        self.slab = _Slab(self.option, self.z_range, self.device_index, self.stream)
         self.car = self.slab.car
         self.dims = self.car.dims
         self.slab_voxels = self.car.slab_voxels
         self._counts = None
+
+    def rebalance(self, my_cost):
+        """Re-partitions the grid so that every slab carries about the same measured cost (call
+        it with this rank's fusion time of a representative pass). The grid state is discarded,
+        like Init(). Returns the new ranges."""
+        if self.world == 1:
+            return self.ranges
+        torch = self.torch
+        mine = torch.tensor([float(my_cost)], dtype=torch.float64, device=self.slab.device)
+        allc = [torch.empty_like(mine) for _ in range(self.world)]
+        torch.distributed.all_gather(allc, mine, group=self.group)
+        cost = [float(t.item()) for t in allc]
+        new = rebalanced_ranges(self.ranges, cost)
+        if new != self.ranges:
+            self.ranges = new
+            self.car.synchronize()
+            self.slab.car.close()
+            self.slab = None
+            self._build()
+        return self.ranges
 
     # ---- carving: no exchange -----------------------------------------------------------------
     def reset(self):
