@@ -233,6 +233,13 @@ int ensure_tiles(vcb_carver* c, int width, int height) {
   return VCB_OK;
 }
 
+// flag storage of one queue slot (NULL when tile classification is off)
+uint32_t* tile_slot(vcb_carver* c, int slot) {
+  if (!c->use_tiles || c->opt.sdf_interp != VCB_INTERP_BILINEAR || !c->tiles.ptr) return nullptr;
+  return reinterpret_cast<uint32_t*>(static_cast<unsigned char*>(c->tiles.ptr) +
+                                     (size_t)slot * c->tile_slot_bytes);
+}
+
 // queues the block-flag kernel for `n` freshly written images and points their views at the flags
 void attach_tiles(vcb_carver* c, const int* slots, const float* const* images, const vcb_view* views,
                   int n) {
@@ -417,6 +424,7 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
       hv[i].scratch = static_cast<unsigned char*>(c->sdf_scratch.ptr) + (size_t)i * c->sdf_scr;
       hv[i].absmax = static_cast<int*>(c->absmax.ptr) + i;
       hv[i].max_out = max_sdf + slot;
+      hv[i].tile_flags = tile_slot(c, slot);  // written by the finalize pass
       hv[i].width = v.width;
       hv[i].height = v.height;
       hv[i].rx0 = v.roi_min[0];
@@ -435,15 +443,11 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
                    c->opt.truncation_band, c->stream, &c->stage_launches[0]);
     }
     CU(c, cudaGetLastError());
-    {
-      int slots[kSdfSubBatch];
-      const float* imgs[kSdfSubBatch];
-      for (int i = 0; i < nb; i++) {
-        slots[i] = c->pending + i;
-        imgs[i] = hv[i].out;
-      }
-      attach_tiles(c, slots, imgs, views + first, nb);
-      CU(c, cudaGetLastError());
+    for (int i = 0; i < nb; i++) {
+      FuseView& f = c->fp.views[c->pending + i];
+      f.tiles = hv[i].tile_flags;
+      f.tile_words = tile_words_for(hv[i].width);
+      f.tile_rows = tile_rows_for(hv[i].height);
     }
     if (!device_io) {
       CU(c, cudaEventRecord(c->ev_consumed[set], c->stream));
@@ -808,6 +812,7 @@ static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width,
   hv.mask = reinterpret_cast<uint8_t*>(base + off_mask);
   hv.out = reinterpret_cast<float*>(base);
   hv.scratch = reinterpret_cast<unsigned char*>(base + off_scr);
+  hv.tile_flags = nullptr;
   hv.absmax = reinterpret_cast<int*>(base + off_misc);
   hv.max_out = reinterpret_cast<float*>(base + off_misc + 64);
   hv.width = width;

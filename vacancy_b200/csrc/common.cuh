@@ -76,6 +76,7 @@ struct SdfView {
   unsigned char* scratch;  // sdf_scratch_bytes(width, height) bytes, 256-byte aligned
   int* absmax;           // scratch: [0] max |D| over the ROI (INT_MAX when some pixel has no seed)
   float* max_out;        // device scalar: max over the final float image
+  uint32_t* tile_flags;  // optional: 8x8-block flags of the final image (see FuseView::tiles)
   int width, height;
   int rx0, ry0, rx1, ry1;
 };

@@ -379,11 +379,37 @@ __global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const __grid_constan
   if (cx == 0 && local_max > 0) atomicMax(v.absmax, local_max);
 }
 
-// ---- pass 3: int -> float, normalisation, truncation, image maximum. Block per group of rows. ---
+// ---- pass 3: int -> float, normalisation, truncation, image maximum, 8x8-block flags. -----------
+// One block per band of 8 image rows, one thread per 8x8-pixel block of the band: 16-byte loads of
+// the int16 distances, 16-byte stores of the floats (when the width allows), and - because a thread
+// owns a whole 8x8 block - the "all texels 1.0f" / "all texels kVal" flags that the fusion kernel
+// uses to classify voxel tiles come for free (one ballot per 32 blocks).
+__device__ __forceinline__ float sdf_value(int d, int mode, bool do_norm, float norm, int truncate,
+                                           float band) {
+  float f;
+  if (mode == kSdfSigned) {
+    f = d == kRowInf ? FLT_MAX : (d == -kRowInf ? -FLT_MAX : (float)d);
+    if (do_norm) f = __fmul_rn(f, norm);
+    if (truncate) {  // voxel_carver.cc:225-236
+      if (-band >= f) {
+        f = kInvalidSdf;
+      } else {
+        const float q = __fdiv_rn(f, band);
+        f = q < 1.0f ? q : 1.0f;
+      }
+    }
+  } else {  // DistanceTransformL1 of the mask itself: foreground distance, others 0
+    f = d < 0 ? (d == -kRowInf ? FLT_MAX : (float)(-d)) : 0.0f;
+  }
+  return f;
+}
+
 __global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant__ SdfBatch B,
                                                            int mode, int normalize, int truncate,
                                                            float band) {
   const SdfView& v = B.v[blockIdx.y];
+  const int y0 = blockIdx.x * kTilePx;
+  if (y0 >= v.height) return;
   float norm = 1.0f;
   bool do_norm = false;
   if (normalize && mode == kSdfSigned) {
@@ -396,34 +422,61 @@ __global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant
   }
   const int pitch = sdf_pitch(v.width);
   const int16_t* __restrict__ cold = view_cold(v);
+  const int nbx = (v.width + kTilePx - 1) / kTilePx;
+  const int words = (nbx + 31) / 32;
+  const bool vec_out = (v.width & 3) == 0;
+  const int lane = threadIdx.x & 31;
   float tmax = -FLT_MAX;
-  for (int y = blockIdx.x; y < v.height; y += gridDim.x) {
-    const bool row_in = y >= v.ry0 && y <= v.ry1;
-    for (int x = threadIdx.x; x < v.width; x += blockDim.x) {
-      float f = 0.0f;  // outside the ROI, voxel_carver.cc:104
-      if (row_in && x >= v.rx0 && x <= v.rx1) {
-        const int d = __ldg(cold + (size_t)y * pitch + x);
-        if (mode == kSdfSigned) {
-          f = d == kRowInf ? FLT_MAX : (d == -kRowInf ? -FLT_MAX : (float)d);
-          if (do_norm) f = __fmul_rn(f, norm);
-          if (truncate) {  // voxel_carver.cc:225-236
-            if (-band >= f) {
-              f = kInvalidSdf;
-            } else {
-              const float q = __fdiv_rn(f, band);
-              f = q < 1.0f ? q : 1.0f;
-            }
+  // the loop bound is rounded up to whole warps so that every lane reaches the ballots
+  for (int bx0 = 0; bx0 < nbx; bx0 += blockDim.x) {
+    const int bx = bx0 + threadIdx.x;
+    const int x0 = bx * kTilePx;
+    bool ones = bx < nbx, kval = bx < nbx;
+    if (bx < nbx) {
+      for (int j = 0; j < kTilePx; j++) {
+        const int y = y0 + j;
+        if (y >= v.height) break;
+        const bool row_in = y >= v.ry0 && y <= v.ry1;
+        float f[kTilePx];
+        // the int16 scratch rows are padded to 32 pixels: the 16-byte load is always in bounds
+        const uint4 raw = row_in ? __ldg(reinterpret_cast<const uint4*>(cold + (size_t)y * pitch + x0))
+                                 : make_uint4(0, 0, 0, 0);
+        const unsigned rw[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+        for (int i = 0; i < kTilePx; i++) {
+          const int x = x0 + i;
+          const int d = (int)(int16_t)((rw[i >> 1] >> (16 * (i & 1))) & 0xffffu);
+          // zeros outside the ROI, voxel_carver.cc:104
+          f[i] = (row_in && x >= v.rx0 && x <= v.rx1)
+                     ? sdf_value(d, mode, do_norm, norm, truncate, band)
+                     : 0.0f;
+          if (x < v.width) {
+            tmax = fmaxf(tmax, f[i]);
+            ones = ones && (f[i] == 1.0f);
+            kval = kval && (f[i] == kInvalidSdf);
           }
-        } else {  // DistanceTransformL1 of the mask itself: foreground distance, others 0
-          f = d < 0 ? (d == -kRowInf ? FLT_MAX : (float)(-d)) : 0.0f;
+        }
+        float* __restrict__ o = v.out + (size_t)y * v.width + x0;
+        if (vec_out && x0 + kTilePx <= v.width) {
+          reinterpret_cast<float4*>(o)[0] = make_float4(f[0], f[1], f[2], f[3]);
+          reinterpret_cast<float4*>(o)[1] = make_float4(f[4], f[5], f[6], f[7]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < kTilePx; i++) {
+            if (x0 + i < v.width) o[i] = f[i];
+          }
         }
       }
-      v.out[(size_t)y * v.width + x] = f;
-      tmax = fmaxf(tmax, f);
+    }
+    const unsigned ow = __ballot_sync(0xffffffffu, ones), kw = __ballot_sync(0xffffffffu, kval);
+    if (v.tile_flags != nullptr && lane == 0 && bx < nbx) {
+      const int nby = (v.height + kTilePx - 1) / kTilePx;
+      v.tile_flags[blockIdx.x * words + (bx >> 5)] = ow;
+      v.tile_flags[(nby + blockIdx.x) * words + (bx >> 5)] = kw;
     }
   }
   for (int o = 16; o > 0; o >>= 1) tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
-  if ((threadIdx.x & 31) == 0) atomic_max_float(v.max_out, tmax);
+  if (lane == 0) atomic_max_float(v.max_out, tmax);
 }
 
 __global__ void __launch_bounds__(256) image_max_kernel(const float* __restrict__ img, int64_t n,
@@ -475,8 +528,8 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
   } else {
     sdf_col_kernel<<<dim3((max_cols + 31) / 32, n_views), dim3(32, kColSegs), 0, stream>>>(views_dev);
   }
-  sdf_finalize_kernel<<<dim3(min(max_h, 1024), n_views), 256, 0, stream>>>(views_dev, mode,
-                                                                            normalize, truncate, band);
+  sdf_finalize_kernel<<<dim3((max_h + kTilePx - 1) / kTilePx, n_views), 256, 0, stream>>>(
+      views_dev, mode, normalize, truncate, band);
   if (launches) *launches += 4;
 }
 
@@ -568,6 +621,7 @@ extern "C" int vcb_make_signed_distance_field_noalloc(
   v.mask = mask_dev;
   v.out = dist_dev;
   v.scratch = scratch + kNoAllocHeader;
+  v.tile_flags = nullptr;
   v.absmax = reinterpret_cast<int*>(scratch + 128);      // both cells are re-initialised by
   v.max_out = reinterpret_cast<float*>(scratch + 192);   // sdf_bits_kernel at the start of a call
   v.width = width;
