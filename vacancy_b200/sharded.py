@@ -252,7 +252,29 @@ class ShardedCarver:
                               masks=True)
 
     def carve_host_masks(self, cameras, host_masks):
-        assert self.car.carve_batch(cameras, host_masks)
+        """Masks in HOST memory (pinned for asynchronous copies). One GPU: straight through the host
+        entry point. Several GPUs: every rank uploads only its 1/world share over its own PCIe link
+        and the shares are all-gathered over NVLink (NCCL), so no rank moves the whole set from the
+        host; then each rank fuses every view into its slab."""
+        if self.world == 1:
+            assert self.car.carve_batch(cameras, host_masks)
+            return
+        torch = self.torch
+        n = len(host_masks)
+        h, w = host_masks[0].shape
+        per = (n + self.world - 1) // self.world
+        buf = getattr(self, "_mask_buf", None)
+        if buf is None or tuple(buf.shape) != (self.world * per, h, w):
+            buf = self._mask_buf = torch.empty((self.world * per, h, w), dtype=torch.uint8,
+                                               device=self.slab.device)
+        with torch.cuda.stream(self.stream):
+            lo, hi = self.rank * per, min(n, (self.rank + 1) * per)
+            for i in range(lo, hi):
+                buf[i].copy_(torch.from_numpy(host_masks[i]), non_blocking=True)
+            torch.distributed.all_gather_into_tensor(buf.view(self.world, -1),
+                                                     buf[lo:lo + per].view(-1), group=self.group)
+        views = self.make_views(cameras, w, h)
+        self.carve_device_masks(views, buf[:n])
 
     # ---- marching cubes ---------------------------------------------------------------------------
     def _sendrecv(self, send, recv):
