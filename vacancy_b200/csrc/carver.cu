@@ -330,6 +330,8 @@ int flush_pending(vcb_carver* c) {
     if (rc != VCB_OK) return rc;
   }
   c->fp.n_views = c->pending;
+  // update_num <= views applied so far, so the `update_num > max` gate cannot fire before that
+  c->fp.cap_possible = c->max_count > (int64_t)c->opt.voxel_max_update_num ? 1 : 0;
   {
     Span span(c, 1);
     launch_fusion(c->fp, c->opt.sdf_interp, c->opt.voxel_update, c->stream, &c->stage_launches[1]);

@@ -63,6 +63,7 @@ struct FuseParams {
   int z_begin, z_end;    // owned planes
   int n_views;
   int max_update_num;
+  int cap_possible;      // host bound: update_num may exceed max_update_num during this launch
   int use_truncation;
   int update_outside;
   float weight;
