@@ -246,9 +246,10 @@ def run_ours(args, cfg):
     if world > 1 and not args.no_rebalance:
         # the slabs do not cost the same (edge slabs see the cameras differently): re-partition once
         # from the measured fusion time of the warm-up passes, then warm up again
-        ranges = car.rebalance(car.stage_times()["fusion"][0])
-        for _ in range(args.warmup):
-            step_resident()
+        for _ in range(2):  # second round refines the first estimate
+            ranges = car.rebalance(car.stage_times()["fusion"][0])
+            for _ in range(args.warmup):
+                step_resident()
     else:
         ranges = car.ranges
     car.stage_times()  # clear the per-stage counters
