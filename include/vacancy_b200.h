@@ -143,6 +143,12 @@ int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t 
                                    const int32_t roi_max[2], int32_t minmax_normalize,
                                    int32_t use_truncation, float truncation_band, float* dist);
 
+/* SignedDistance2Color (voxel_carver.h:127-128, voxel_carver.cc:239-267): the debugging colour map of
+ * a 2D SDF, HOST float image in, HOST RGB image (3 bytes per pixel) out; positive distances fade
+ * from white to red, the others from white to blue. Requires min_negative_d < 0 < max_positive_d. */
+int vcb_signed_distance_to_color(int32_t device, const float* sdf, int32_t width, int32_t height,
+                                 float min_negative_d, float max_positive_d, uint8_t* rgb);
+
 /* No counterpart in the reference: MakeSignedDistanceField for callers that must not allocate.
  * Some hosts cannot let a library call cudaMalloc once they are running: an application whose
  * own arena has claimed the GPU's memory (a driver allocation may then fail, or fragment what is

@@ -120,6 +120,8 @@ class RefLib:
         L.ref_time_make_sdf.restype = C.c_double
         L.ref_time_make_sdf.argtypes = [c_u8_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                         C.c_int]
+        L.ref_signed_distance_to_color.argtypes = [c_float_p, C.c_int, C.c_int, C.c_float, C.c_float,
+                                                   c_u8_p]
         L.ref_w2c_from_c2w.argtypes = [c_double_p, c_float_p]
         L.ref_tum_pose_to_c2w.argtypes = [c_double_p, c_double_p, c_double_p]
         L.ref_pinhole_ray_c.argtypes = [C.c_int, C.c_int] + [C.c_float] * 6 + [c_float_p]
@@ -150,6 +152,14 @@ class RefLib:
         out = np.empty((h, w), np.float32)
         self.L.ref_make_sdf(_p(mask, c_u8_p), w, h, *roi, int(normalize), int(truncate),
                             C.c_float(band), _p(out, c_float_p))
+        return out
+
+    def signed_distance_to_color(self, sdf, min_negative_d, max_positive_d):
+        sdf = np.ascontiguousarray(sdf, np.float32)
+        h, w = sdf.shape
+        out = np.empty((h, w, 3), np.uint8)
+        self.L.ref_signed_distance_to_color(_p(sdf, c_float_p), w, h, C.c_float(min_negative_d),
+                                            C.c_float(max_positive_d), _p(out, c_u8_p))
         return out
 
     def time_make_sdf(self, mask, normalize, truncate, band, reps):
@@ -302,6 +312,8 @@ class PortLib:
         L.vo_w2c_from_c2w.argtypes = [c_double_p, c_float_p]
         L.vo_distance_transform_l1.argtypes = [c_u8_p] + [C.c_int] * 6 + [c_float_p]
         L.vo_make_sdf.argtypes = [c_u8_p] + [C.c_int] * 8 + [C.c_float, c_float_p]
+        L.vo_signed_distance_to_color.argtypes = [c_float_p, C.c_int, C.c_int, C.c_float, C.c_float,
+                                                  c_u8_p]
         L.vo_grid_dims.argtypes = [OP, c_int_p]
         L.vo_grid_positions.argtypes = [OP, c_float_p, c_float_p, c_float_p]
         L.vo_grid_reset.argtypes = [c_float_p, c_int_p, C.c_int64]
@@ -337,6 +349,14 @@ class PortLib:
         out = np.empty((h, w), np.float32)
         self.L.vo_make_sdf(_p(mask, c_u8_p), w, h, *roi, int(normalize), int(truncate),
                            C.c_float(band), _p(out, c_float_p))
+        return out
+
+    def signed_distance_to_color(self, sdf, min_negative_d, max_positive_d):
+        sdf = np.ascontiguousarray(sdf, np.float32)
+        h, w = sdf.shape
+        out = np.empty((h, w, 3), np.uint8)
+        self.L.vo_signed_distance_to_color(_p(sdf, c_float_p), w, h, C.c_float(min_negative_d),
+                                           C.c_float(max_positive_d), _p(out, c_u8_p))
         return out
 
     def w2c_from_c2w(self, c2w):

@@ -117,6 +117,17 @@ void ref_make_sdf(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1,
   std::memcpy(out, d.data().data(), sizeof(float) * w * h);
 }
 
+// voxel_carver.cc:239-267
+void ref_signed_distance_to_color(const float* sdf, int w, int h, float min_negative_d,
+                                  float max_positive_d, uint8_t* rgb) {
+  vacancy::Image1f img;
+  img.Init(w, h, 0.0f);
+  std::memcpy(img.data_ptr()->data(), sdf, sizeof(float) * w * h);
+  vacancy::Image3b vis;
+  vacancy::SignedDistance2Color(img, &vis, min_negative_d, max_positive_d);
+  std::memcpy(rgb, vis.data().data(), static_cast<size_t>(w) * h * 3);
+}
+
 // Times `reps` calls of MakeSignedDistanceField on an already-built Image1b; seconds.
 double ref_time_make_sdf(const uint8_t* mask, int w, int h, int normalize,
                          int truncate, float band, int reps) {

@@ -151,6 +151,28 @@ void vo_make_sdf(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1, i
   free(pos);
 }
 
+/* voxel_carver.cc:239-267 */
+void vo_signed_distance_to_color(const float* sdf, int w, int h, float min_negative_d,
+                                 float max_positive_d, uint8_t* rgb) {
+  size_t i, n = (size_t)w * (size_t)h;
+  for (i = 0; i < n; i++) {
+    float d = sdf[i];
+    if (d > 0) {
+      float t = (max_positive_d - d) / max_positive_d;
+      t = fminf2(fmaxf2(t, 0.0f), 1.0f);
+      rgb[3 * i + 0] = (uint8_t)255;
+      rgb[3 * i + 1] = (uint8_t)(255 * t);
+      rgb[3 * i + 2] = (uint8_t)(255 * t);
+    } else {
+      float t = (d - min_negative_d) / (-min_negative_d);
+      t = fminf2(fmaxf2(t, 0.0f), 1.0f);
+      rgb[3 * i + 0] = (uint8_t)(255 * t);
+      rgb[3 * i + 1] = (uint8_t)(255 * t);
+      rgb[3 * i + 2] = (uint8_t)255;
+    }
+  }
+}
+
 /* ---- grid ----------------------------------------------------------------------------------- */
 
 /* voxel_carver.cc:375-389 (option checks) and :276-301 (grid checks and sizing) */

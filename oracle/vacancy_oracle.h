@@ -54,6 +54,10 @@ void vo_distance_transform_l1(const uint8_t* mask, int w, int h, int rx0, int ry
 void vo_make_sdf(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1, int ry1,
                  int normalize, int truncate, float band, float* out);
 
+/* SignedDistance2Color, voxel_carver.cc:239-267; rgb = 3 bytes per pixel */
+void vo_signed_distance_to_color(const float* sdf, int w, int h, float min_negative_d,
+                                 float max_positive_d, uint8_t* rgb);
+
 /* VoxelCarver::Init + VoxelGrid::Init validation and sizing, voxel_carver.cc:276-301,375-389.
  * Returns 1 on success (dims filled), 0 when the reference would return false. */
 int vo_grid_dims(const vo_options* opt, int* dims3);

@@ -333,3 +333,15 @@ def test_cfg3_slab_weighted_against_compiled_reference(cuda_lib, ref):
     (gs, gn), (ws, wn) = car.download_grid(), rc.download()
     assert np.array_equal(gn, wn) and bits_equal(gs, ws)
     H.assert_mesh_equal(car.ExtractIsoSurface(), rc.extract_iso(), opt.bb_min, opt.bb_max)
+
+
+def test_sdf_color_map(cuda_lib, port, bunny):
+    """SignedDistance2Color on the device, byte-exact against the oracle."""
+    from vacancy_b200 import signed_distance_to_color
+    rng = np.random.default_rng(4)
+    imgs = [bunny.final["sdf2d_view0"], rng.normal(scale=0.7, size=(61, 47)).astype(np.float32),
+            make_signed_distance_field(bunny.masks[3], use_truncation=True)]
+    for img in imgs:
+        for lo, hi in ((-1.0, 1.0), (-0.3, 2.5)):
+            assert np.array_equal(signed_distance_to_color(img, lo, hi),
+                                  port.signed_distance_to_color(img, lo, hi))

@@ -57,3 +57,15 @@ def test_examples_cc_unchanged_through_shim(tmp_path):
     vb, fb, _ = read_ply(os.path.join(b, "voxel_00005.ply"))
     assert np.array_equal(fa, fb) and va.shape == vb.shape == (28475 * 24, 3)
     assert np.abs(va - vb).max() <= 1e-5 * diag
+
+
+def test_pointer_batch_overload(tmp_path):
+    """vacancy_b200::CarveBatch (include/vacancy_b200_batch.h): all six bunny views in one call from
+    C++ host code give the reference's final mesh and cube counts."""
+    demo = os.path.join(REF_DIR, "batch_demo_b200")
+    if not os.path.exists(demo):
+        pytest.skip("prebuilt batch demo not present under oracle/_ref")
+    r = subprocess.run([demo, os.path.join(REF_DIR, "data") + "/"], capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.split() == ["8672", "17270", "28475"]

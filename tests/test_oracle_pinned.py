@@ -200,3 +200,14 @@ def test_marching_cubes_on_handmade_grids_vs_reference(ref, port):
         for inside_empty in (False, True):
             assert np.array_equal(cr.extract_voxel(inside_empty)[1],
                                   cp.extract_voxel(inside_empty)[1])
+
+
+def test_sdf_color_map_vs_reference(ref, port, bunny):
+    """SignedDistance2Color (voxel_carver.cc:239-267): oracle restatement == compiled reference."""
+    rng = np.random.default_rng(3)
+    imgs = [bunny.final["sdf2d_view0"], rng.normal(scale=0.7, size=(37, 53)).astype(np.float32),
+            np.zeros((4, 5), np.float32)]
+    for img in imgs:
+        for lo, hi in ((-1.0, 1.0), (-0.3, 2.5)):
+            assert np.array_equal(ref.signed_distance_to_color(img, lo, hi),
+                                  port.signed_distance_to_color(img, lo, hi))

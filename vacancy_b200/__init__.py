@@ -10,4 +10,4 @@ from .capi import LibraryMissing, VcbError, load_library  # noqa: F401
 from .carver import (Camera, OrthoCamera, PinholeCamera, SdfInterpolation,  # noqa: F401
                      UpdateOutsideImage, VoxelCarver, VoxelCarverOption, VoxelUpdate,
                      VoxelUpdateOption, distance_transform_l1, make_signed_distance_field,
-                     w2c_from_c2w)
+                     signed_distance_to_color, w2c_from_c2w)

@@ -38,7 +38,7 @@ EXPORTS = [
     "vcb_grid_dims", "vcb_slab_range", "vcb_grid_positions", "vcb_set_stream", "vcb_synchronize",
     "vcb_flush", "vcb_carve_masks", "vcb_carve_masks_device", "vcb_carve_sdfs",
     "vcb_carve_sdfs_device", "vcb_distance_transform_l1", "vcb_make_signed_distance_field",
-    "vcb_make_signed_distance_field_noalloc",
+    "vcb_make_signed_distance_field_noalloc", "vcb_signed_distance_to_color",
     "vcb_extract_iso_count", "vcb_extract_iso_fill", "vcb_extract_iso_device",
     "vcb_extract_iso_begin", "vcb_extract_iso_vertices", "vcb_extract_iso_export_top",
     "vcb_extract_iso_import_bottom", "vcb_extract_iso_faces", "vcb_halo_device",
@@ -86,6 +86,7 @@ def load_library(path=LIB_PATH):
                                                  fp]
     L.vcb_make_signed_distance_field_noalloc.argtypes = [i32, vp, i32, i32, ip, ip, i32, i32,
                                                          C.c_float, vp, vp]
+    L.vcb_signed_distance_to_color.argtypes = [i32, fp, i32, i32, C.c_float, C.c_float, u8p]
     L.vcb_extract_iso_count.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
     L.vcb_extract_iso_begin.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
     L.vcb_extract_iso_vertices.argtypes = [vp, i64]

@@ -396,3 +396,15 @@ def make_signed_distance_field(mask, roi_min=None, roi_max=None, minmax_normaliz
         int(minmax_normalize), int(use_truncation), C.c_float(truncation_band),
         out.ctypes.data_as(C.POINTER(C.c_float))))
     return out
+
+
+def signed_distance_to_color(sdf, min_negative_d, max_positive_d, device=0):
+    """SignedDistance2Color (voxel_carver.h:127-128) on the GPU: float32 [H, W] -> uint8 [H, W, 3]."""
+    L = capi.load_library()
+    sdf = np.ascontiguousarray(sdf, np.float32)
+    h, w = sdf.shape
+    out = np.empty((h, w, 3), np.uint8)
+    capi.check(L, None, L.vcb_signed_distance_to_color(
+        device, sdf.ctypes.data_as(C.POINTER(C.c_float)), w, h, C.c_float(min_negative_d),
+        C.c_float(max_positive_d), out.ctypes.data_as(C.POINTER(C.c_uint8))))
+    return out

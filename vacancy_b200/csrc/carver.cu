@@ -834,6 +834,31 @@ static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width,
   return VCB_OK;
 }
 
+int vcb_signed_distance_to_color(int32_t device, const float* sdf, int32_t width, int32_t height,
+                                 float min_negative_d, float max_positive_d, uint8_t* rgb) {
+  if (!sdf || !rgb) return fail(nullptr, VCB_ERR_INVALID, "null argument");
+  if (width < 1 || height < 1) return fail(nullptr, VCB_ERR_INVALID, "empty image");
+  if (!(min_negative_d < 0.0f) || !(0.0f < max_positive_d))  // the reference asserts these
+    return fail(nullptr, VCB_ERR_INVALID, "need min_negative_d < 0 < max_positive_d");
+  int rc = use_device(nullptr, device);
+  if (rc != VCB_OK) return rc;
+  const size_t n = (size_t)width * height;
+  Scratch buf;
+  const size_t off_rgb = (n * sizeof(float) + 255) & ~(size_t)255;
+  CU(nullptr, buf.reserve(off_rgb + n * 3));
+  char* base = static_cast<char*>(buf.ptr);
+  cudaError_t e = cudaMemcpy(base, sdf, n * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    launch_sdf_color(reinterpret_cast<const float*>(base), (int64_t)n, min_negative_d,
+                     max_positive_d, reinterpret_cast<uint8_t*>(base + off_rgb), nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(rgb, base + off_rgb, n * 3, cudaMemcpyDeviceToHost);
+  buf.release();
+  if (e != cudaSuccess) return fail(nullptr, VCB_ERR_CUDA, "SignedDistance2Color: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
 int vcb_distance_transform_l1(int32_t device, const uint8_t* mask, int32_t width, int32_t height,
                               const int32_t roi_min[2], const int32_t roi_max[2], float* dist) {
   return sdf_free_function(device, mask, width, height, roi_min, roi_max, kSdfDistanceL1, 0, 0,

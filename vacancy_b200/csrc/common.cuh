@@ -93,6 +93,8 @@ struct SdfBatch {
 
 void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normalize, int truncate,
                   float band, cudaStream_t stream, int64_t* launches);
+void launch_sdf_color(const float* sdf, int64_t n, float min_neg, float max_pos, uint8_t* rgb,
+                      cudaStream_t stream);
 void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_t stream,
                       int64_t* launches);
 void launch_fusion(FuseParams& p, int interp, int update, cudaStream_t stream,

@@ -496,6 +496,36 @@ __global__ void __launch_bounds__(256) image_max_kernel(const float* __restrict_
 
 __global__ void set_float_kernel(float* p, float v) { *p = v; }
 
+// voxel_carver.cc:246-265, one pixel per thread; the uint8 conversions truncate like static_cast
+__global__ void __launch_bounds__(256) sdf_color_kernel(const float* __restrict__ sdf, int64_t n,
+                                                        float min_neg, float max_pos,
+                                                        uint8_t* __restrict__ rgb) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float d = sdf[i];
+  uint8_t r, g, b;
+  if (d > 0.0f) {
+    float t = __fdiv_rn(__fsub_rn(max_pos, d), max_pos);
+    t = t < 0.0f ? 0.0f : t;  // std::max(t, 0.0f)
+    t = 1.0f < t ? 1.0f : t;  // std::min(., 1.0f)
+    const uint8_t c = (uint8_t)__fmul_rn(255.0f, t);
+    r = 255;
+    g = c;
+    b = c;
+  } else {
+    float t = __fdiv_rn(__fsub_rn(d, min_neg), -min_neg);
+    t = t < 0.0f ? 0.0f : t;
+    t = 1.0f < t ? 1.0f : t;
+    const uint8_t c = (uint8_t)__fmul_rn(255.0f, t);
+    r = c;
+    g = c;
+    b = 255;
+  }
+  rgb[3 * i + 0] = r;
+  rgb[3 * i + 1] = g;
+  rgb[3 * i + 2] = b;
+}
+
 }  // namespace
 
 void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normalize, int truncate,
@@ -531,6 +561,11 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
   sdf_finalize_kernel<<<dim3((max_h + kTilePx - 1) / kTilePx, n_views), 256, 0, stream>>>(
       views_dev, mode, normalize, truncate, band);
   if (launches) *launches += 4;
+}
+
+void launch_sdf_color(const float* sdf, int64_t n, float min_neg, float max_pos, uint8_t* rgb,
+                      cudaStream_t stream) {
+  sdf_color_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(sdf, n, min_neg, max_pos, rgb);
 }
 
 void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_t stream,

@@ -7,8 +7,8 @@
 // What runs where: DistanceTransformL1 / MakeSignedDistanceField, Carve, ExtractVoxel and
 // ExtractIsoSurface run on the GPU through the C ABI, with no CPU fallback - if the library
 // reports an error the call logs it with LOGE and returns false (or leaves the mesh empty), the
-// reference's own error convention.  SignedDistance2Color (a debugging colour
-// map, not on the carving path) and the small VoxelGrid value class stay ordinary host code.
+// reference's own error convention.  Only the small VoxelGrid value class stays
+// ordinary host code.
 //
 // The reference class has no member that could hold a device handle (voxel_carver.h:95-97), and the
 // header must not change, so carvers are tracked in a side table keyed by `this`; the AoS
@@ -21,6 +21,7 @@
 #include <unordered_map>
 
 #include "vacancy_b200.h"
+#include "vacancy_b200_batch.h"
 
 namespace {
 
@@ -117,26 +118,16 @@ void MakeSignedDistanceField(const Image1b& mask, const Eigen::Vector2i& roi_min
          "MakeSignedDistanceField");
 }
 
-// Debugging colour map (examples.cc:131-133); host code, outside the accelerated path.
-// Positive distances fade from white to red, negative ones from white to blue.
+// Debugging colour map (examples.cc:131-133), voxel_carver.cc:239-267
 void SignedDistance2Color(const Image1f& sdf, Image3b* vis_sdf, float min_negative_d,
                           float max_positive_d) {
   assert(min_negative_d < 0 && 0 < max_positive_d && vis_sdf != nullptr);
   vis_sdf->Init(sdf.width(), sdf.height());
-  const float* src = sdf.data().data();
-  uint8_t* dst = vis_sdf->data_ptr()->data();
-  const size_t n = static_cast<size_t>(sdf.width()) * sdf.height();
-  for (size_t i = 0; i < n; i++) {
-    const float d = src[i];
-    const bool positive = d > 0;
-    float t = positive ? (max_positive_d - d) / max_positive_d
-                       : (d - min_negative_d) / (-min_negative_d);
-    t = std::min(std::max(t, 0.0f), 1.0f);
-    const uint8_t faded = static_cast<uint8_t>(255 * t);
-    dst[3 * i + 0] = positive ? 255 : faded;
-    dst[3 * i + 1] = faded;
-    dst[3 * i + 2] = positive ? faded : 255;
-  }
+  report(nullptr,
+         vcb_signed_distance_to_color(device_ordinal(), sdf.data().data(), sdf.width(),
+                                      sdf.height(), min_negative_d, max_positive_d,
+                                      vis_sdf->data_ptr()->data()),
+         "SignedDistance2Color");
 }
 
 // ---- Voxel / VoxelGrid: plain host value types kept for source compatibility ----------------------
@@ -333,3 +324,33 @@ void VoxelCarver::ExtractIsoSurface(Mesh* mesh, double iso_level, bool linear_in
 }
 
 }  // namespace vacancy
+
+namespace vacancy_b200 {
+
+bool CarveBatch(vacancy::VoxelCarver* carver, const std::vector<const vacancy::Camera*>& cameras,
+                const std::vector<const vacancy::Image1b*>& silhouettes) {
+  if (carver == nullptr || cameras.size() != silhouettes.size()) {
+    vacancy::LOGE("CarveBatch: need a carver and as many cameras as silhouettes\n");
+    return false;
+  }
+  vcb_carver* h = find_carver(carver);
+  if (h == nullptr) {
+    vacancy::LOGE("VoxelCarver::Carve voxel grid has not been initialized\n");
+    return false;
+  }
+  std::vector<vcb_view> views(cameras.size());
+  std::vector<const uint8_t*> masks(cameras.size());
+  for (size_t i = 0; i < cameras.size(); i++) {
+    const vacancy::Image1b& m = *silhouettes[i];
+    if (!make_view(*cameras[i], m.width(), m.height(), Eigen::Vector2i(0, 0),
+                   Eigen::Vector2i(m.width() - 1, m.height() - 1), &views[i])) {
+      return false;
+    }
+    masks[i] = m.data().data();
+  }
+  return report(h, vcb_carve_masks(h, static_cast<int32_t>(views.size()), views.data(),
+                                   masks.data(), nullptr),
+                "CarveBatch");
+}
+
+}  // namespace vacancy_b200
