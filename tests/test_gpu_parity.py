@@ -345,3 +345,44 @@ def test_sdf_color_map(cuda_lib, port, bunny):
         for lo, hi in ((-1.0, 1.0), (-0.3, 2.5)):
             assert np.array_equal(signed_distance_to_color(img, lo, hi),
                                   port.signed_distance_to_color(img, lo, hi))
+
+
+def test_error_paths_through_the_abi(cuda_lib, port):
+    """Argument errors are reported through status codes + vcb_last_error, never by a fallback."""
+    import ctypes as C
+    from vacancy_b200 import capi, Camera
+    from vacancy_b200.carver import make_view
+    o = S.grid_option(16)
+    car = VoxelCarver(o)
+    assert car.Init()
+    cam = S.circle_cameras(1, 32)[0]
+    mask = np.zeros((32, 32), np.uint8)
+    L, h = car._lib, car._h
+
+    def carve(view):
+        arr = (C.c_void_p * 1)(mask.ctypes.data)
+        return L.vcb_carve_masks(h, 1, C.byref(view), arr, None)
+
+    v = make_view(cam, 32, 32, (0, 0, 32, 31))  # ROI one column beyond the image
+    assert carve(v) == -1 and b"roi" in L.vcb_last_error(h)
+    v = make_view(cam, 32, 32, (5, 0, 4, 31))  # empty ROI
+    assert carve(v) == -1
+    v = make_view(cam, 32, 32)
+    v.model = 7  # not one of the reference's two concrete cameras
+    assert carve(v) == -4 and b"pinhole and ortho" in L.vcb_last_error(h)
+    v = make_view(cam, 32, 32)
+    v.width = 20000  # beyond the int16 distance range of the 2D SDF passes
+    assert carve(v) == -1
+    # an abstract Camera (no projection model) cannot be carved with
+    with pytest.raises(capi.VcbError):
+        car.Carve(Camera(32, 32), mask)
+    # fill before count
+    buf = np.empty(16, np.float32)
+    rc = L.vcb_extract_iso_fill(h, buf.ctypes.data_as(C.POINTER(C.c_float)), None)
+    assert rc == -3 and b"has not run" in L.vcb_last_error(h)
+    # nothing above left a trace in the grid
+    sdf, un = car.download_grid()
+    assert (un == 0).all() and (sdf == port.invalid_sdf()).all()
+    # slab outside the grid
+    bad = VoxelCarver(o, z_range=(10, 40))
+    assert bad.Init() is False and "slab" in bad.last_error
