@@ -29,6 +29,10 @@
 extern "C" {
 #endif
 
+/* Bumped whenever a struct below changes size or layout; compare with vcb_abi_version() before
+ * the first call when the library and the host code are built separately. */
+#define VCB_ABI_VERSION 2
+
 typedef enum vcb_status {
   VCB_OK = 0,
   VCB_ERR_INVALID = -1,   /* bad argument / option the reference's Init() would reject */
@@ -41,6 +45,11 @@ typedef enum vcb_status {
 enum { VCB_UPDATE_MAX = 0, VCB_UPDATE_WEIGHTED_AVERAGE = 1 };
 enum { VCB_INTERP_NN = 0, VCB_INTERP_BILINEAR = 1 };
 enum { VCB_OUTSIDE_NONE = 0, VCB_OUTSIDE_MAX = 1 };
+/* Metric of the 2D silhouette distance. L1 (city block) is what the reference computes
+ * (DistanceTransformL1, voxel_carver.cc:102-167) and the only mode with reference parity; L2 is the
+ * exact Euclidean distance transform, an addition of this library (everything downstream - sign
+ * convention, min/max normalisation, truncation, fusion - is unchanged). */
+enum { VCB_METRIC_L1 = 0, VCB_METRIC_L2 = 1 };
 /* concrete camera models, camera.h:66 (PinholeCamera) and camera.h:116 (OrthoCamera) */
 enum { VCB_CAMERA_PINHOLE = 0, VCB_CAMERA_ORTHO = 1 };
 
@@ -62,6 +71,7 @@ typedef struct vcb_options {
   int32_t device;  /* CUDA device ordinal (default 0) */
   int32_t z_begin; /* this carver owns the z planes [z_begin, z_end) of the global grid; */
   int32_t z_end;   /* z_begin == z_end == 0 selects the whole grid (single GPU) */
+  int32_t sdf_metric; /* VCB_METRIC_L1 (default, the reference's transform) or VCB_METRIC_L2 */
 } vcb_options;
 
 /* One view: camera.w2c().cast<float>() (voxel_carver.cc:438) as a row-major 3x4, the projection
@@ -81,6 +91,9 @@ typedef struct vcb_carver vcb_carver;
 /* Text of the last error on this carver; with NULL, of the last failed vcb_create / free call
  * of the calling thread. Never NULL. */
 const char* vcb_last_error(const vcb_carver* c);
+
+/* VCB_ABI_VERSION the library was built with */
+int vcb_abi_version(void);
 
 /* InvalidSdf::kVal, voxel_carver.cc:100 */
 float vcb_invalid_sdf(void);
@@ -142,6 +155,16 @@ int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t 
                                    int32_t height, const int32_t roi_min[2],
                                    const int32_t roi_max[2], int32_t minmax_normalize,
                                    int32_t use_truncation, float truncation_band, float* dist);
+
+/* No counterpart in the reference: MakeSignedDistanceField with the exact Euclidean metric. For a
+ * foreground (== 255) pixel the value is minus the distance between pixel centres to the nearest
+ * other pixel of the ROI, for any other pixel plus the distance to the nearest foreground pixel;
+ * distances are sqrt(integer) evaluated in float64 and rounded to float32; -+FLT_MAX when the ROI
+ * holds no pixel of the other class. Normalisation and truncation as in voxel_carver.cc:205-236. */
+int vcb_make_signed_distance_field_l2(int32_t device, const uint8_t* mask, int32_t width,
+                                      int32_t height, const int32_t roi_min[2],
+                                      const int32_t roi_max[2], int32_t minmax_normalize,
+                                      int32_t use_truncation, float truncation_band, float* dist);
 
 /* SignedDistance2Color (voxel_carver.h:127-128, voxel_carver.cc:239-267): the debugging colour map of
  * a 2D SDF, HOST float image in, HOST RGB image (3 bytes per pixel) out; positive distances fade

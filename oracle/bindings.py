@@ -314,6 +314,7 @@ class PortLib:
         L.vo_make_sdf.argtypes = [c_u8_p] + [C.c_int] * 8 + [C.c_float, c_float_p]
         L.vo_signed_distance_to_color.argtypes = [c_float_p, C.c_int, C.c_int, C.c_float, C.c_float,
                                                   c_u8_p]
+        L.vo_make_sdf_l2.argtypes = [c_u8_p] + [C.c_int] * 8 + [C.c_float, c_float_p]
         L.vo_grid_dims.argtypes = [OP, c_int_p]
         L.vo_grid_positions.argtypes = [OP, c_float_p, c_float_p, c_float_p]
         L.vo_grid_reset.argtypes = [c_float_p, c_int_p, C.c_int64]
@@ -357,6 +358,16 @@ class PortLib:
         out = np.empty((h, w, 3), np.uint8)
         self.L.vo_signed_distance_to_color(_p(sdf, c_float_p), w, h, C.c_float(min_negative_d),
                                            C.c_float(max_positive_d), _p(out, c_u8_p))
+        return out
+
+    def make_sdf_l2(self, mask, roi=None, normalize=True, truncate=False, band=0.1):
+        """Euclidean variant (not in the reference)."""
+        mask = np.ascontiguousarray(mask, dtype=np.uint8)
+        h, w = mask.shape
+        roi = roi or (0, 0, w - 1, h - 1)
+        out = np.empty((h, w), np.float32)
+        self.L.vo_make_sdf_l2(_p(mask, c_u8_p), w, h, *roi, int(normalize), int(truncate),
+                              C.c_float(band), _p(out, c_float_p))
         return out
 
     def w2c_from_c2w(self, c2w):

@@ -151,6 +151,115 @@ void vo_make_sdf(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1, i
   free(pos);
 }
 
+/* Exact squared Euclidean distance to the nearest pixel with seed[i] != 0 inside the ROI, for every
+ * ROI pixel (-1 when there is none): 1-D distances along the rows, then the lower envelope of
+ * parabolas along each column (Meijster, Roerdink, Hesselink 2000), integers only. */
+static void edt_squared(const uint8_t* seed, int w, int rx0, int ry0, int rx1, int ry1,
+                        long long* d2) {
+  const int rw = rx1 - rx0 + 1, rh = ry1 - ry0 + 1;
+  const long long INF = 1LL << 40;
+  long long* g = (long long*)malloc((size_t)rw * rh * sizeof(long long));
+  int* s = (int*)malloc((size_t)rh * sizeof(int));
+  int* t = (int*)malloc((size_t)rh * sizeof(int));
+  int x, y;
+  for (y = 0; y < rh; y++) { /* nearest seed along the row */
+    long long last = -INF;
+    for (x = 0; x < rw; x++) {
+      if (AT(seed, w, rx0 + x, ry0 + y)) last = x;
+      g[(size_t)y * rw + x] = x - last;
+    }
+    last = INF;
+    for (x = rw - 1; x >= 0; x--) {
+      if (AT(seed, w, rx0 + x, ry0 + y)) last = x;
+      if (last - x < g[(size_t)y * rw + x]) g[(size_t)y * rw + x] = last - x;
+    }
+  }
+  for (x = 0; x < rw; x++) {
+    int q = -1, u;
+#define G2(i) (g[(size_t)(i) * rw + x] * g[(size_t)(i) * rw + x])
+#define F(px, i) (((long long)(px) - (i)) * ((long long)(px) - (i)) + G2(i))
+    for (u = 0; u < rh; u++) {
+      if (g[(size_t)u * rw + x] >= INF / 2) continue;
+      while (q >= 0 && F(t[q], s[q]) > F(t[q], u)) q--;
+      if (q < 0) {
+        q = 0;
+        s[0] = u;
+        t[0] = 0;
+      } else {
+        long long num = (long long)u * u - (long long)s[q] * s[q] + G2(u) - G2(s[q]);
+        long long wv = 1 + num / (2 * (u - s[q]));
+        if (wv < rh) {
+          q++;
+          s[q] = u;
+          t[q] = (int)wv;
+        }
+      }
+    }
+    for (u = rh - 1; u >= 0; u--) {
+      d2[(size_t)(ry0 + u) * w + (rx0 + x)] = q >= 0 ? F(u, s[q]) : -1;
+      if (q >= 0 && u == t[q]) q--;
+    }
+#undef F
+#undef G2
+  }
+  free(g);
+  free(s);
+  free(t);
+}
+
+void vo_make_sdf_l2(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1, int ry1,
+                    int normalize, int truncate, float band, float* dist) {
+  size_t n = (size_t)w * (size_t)h, i;
+  int x, y;
+  uint8_t* fg = (uint8_t*)malloc(n ? n : 1);
+  uint8_t* bg = (uint8_t*)malloc(n ? n : 1);
+  long long* to_bg = (long long*)malloc((n ? n : 1) * sizeof(long long));
+  long long* to_fg = (long long*)malloc((n ? n : 1) * sizeof(long long));
+  for (i = 0; i < n; i++) {
+    fg[i] = mask[i] == 255;
+    bg[i] = !fg[i];
+    dist[i] = 0.0f;
+  }
+  edt_squared(bg, w, rx0, ry0, rx1, ry1, to_bg);
+  edt_squared(fg, w, rx0, ry0, rx1, ry1, to_fg);
+  for (y = ry0; y <= ry1; y++) {
+    for (x = rx0; x <= rx1; x++) {
+      long long d2 = AT(fg, w, x, y) ? AT(to_bg, w, x, y) : AT(to_fg, w, x, y);
+      float e = d2 < 0 ? FLT_MAX : (float)sqrt((double)d2);
+      AT(dist, w, x, y) = AT(fg, w, x, y) ? -e : e;
+    }
+  }
+  if (normalize && n > 0) { /* as voxel_carver.cc:205-222 */
+    float mx = dist[0], mn = dist[0], abs_max;
+    for (i = 1; i < n; i++) {
+      if (mx < dist[i]) mx = dist[i];
+      if (dist[i] < mn) mn = dist[i];
+    }
+    abs_max = fmaxf2(fabsf(mx), fabsf(mn));
+    if (abs_max > FLT_MIN) {
+      float norm = 1.0f / abs_max;
+      for (y = ry0; y <= ry1; y++)
+        for (x = rx0; x <= rx1; x++) AT(dist, w, x, y) *= norm;
+    }
+  }
+  if (truncate) { /* as voxel_carver.cc:225-236 */
+    for (y = ry0; y <= ry1; y++) {
+      for (x = rx0; x <= rx1; x++) {
+        float* d = &AT(dist, w, x, y);
+        if (-band >= *d) {
+          *d = -FLT_MAX;
+        } else {
+          *d = fminf2(1.0f, *d / band);
+        }
+      }
+    }
+  }
+  free(fg);
+  free(bg);
+  free(to_bg);
+  free(to_fg);
+}
+
 /* voxel_carver.cc:239-267 */
 void vo_signed_distance_to_color(const float* sdf, int w, int h, float min_negative_d,
                                  float max_positive_d, uint8_t* rgb) {

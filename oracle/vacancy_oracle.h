@@ -54,6 +54,14 @@ void vo_distance_transform_l1(const uint8_t* mask, int w, int h, int rx0, int ry
 void vo_make_sdf(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1, int ry1,
                  int normalize, int truncate, float band, float* out);
 
+/* NOT in the reference: the same signed field with the exact Euclidean metric (the product's opt-in
+ * VCB_METRIC_L2). Checker for that mode only; pinned against scipy.ndimage.distance_transform_edt and
+ * a brute-force search in tests/test_oracle_pinned.py, not against the reference (which is L1).
+ * Distance = (float)sqrt((double)squared integer distance); sign, FLT_MAX convention, normalisation
+ * and truncation as in vo_make_sdf. */
+void vo_make_sdf_l2(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1, int ry1,
+                    int normalize, int truncate, float band, float* out);
+
 /* SignedDistance2Color, voxel_carver.cc:239-267; rgb = 3 bytes per pixel */
 void vo_signed_distance_to_color(const float* sdf, int w, int h, float min_negative_d,
                                  float max_positive_d, uint8_t* rgb);

@@ -34,8 +34,8 @@ def test_header_symbols_exported(lib):
 
 
 def test_struct_layout(lib):
-    # sizeof(vcb_options) == 72, sizeof(vcb_view) == 92 (checked against a C compile of the header)
-    assert C.sizeof(capi.Options) == 72
+    # sizeof(vcb_options) == 76, sizeof(vcb_view) == 92 (checked against a C compile of the header)
+    assert C.sizeof(capi.Options) == 76
     assert C.sizeof(capi.View) == 92
     o = capi.Options()
     lib.vcb_options_default(C.byref(o))

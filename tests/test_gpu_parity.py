@@ -386,3 +386,44 @@ def test_error_paths_through_the_abi(cuda_lib, port):
     # slab outside the grid
     bad = VoxelCarver(o, z_range=(10, 40))
     assert bad.Init() is False and "slab" in bad.last_error
+
+
+def test_euclidean_metric_option(cuda_lib, port):
+    """VCB_METRIC_L2 (an addition; the reference is L1): the 2D field equals the Euclidean checker
+    bit for bit, and a carve with that option equals the oracle's fusion of those images."""
+    from vacancy_b200 import SdfMetric
+    rng = np.random.default_rng(33)
+    for kind in ("blobs", "noise", "grey", "full", "empty"):
+        for t in range(6):
+            h, w = int(rng.integers(1, 140)), int(rng.integers(1, 140))
+            mask = H.random_mask(rng, h, w, kind)
+            roi = None
+            if t % 3 == 1:
+                x0, y0 = int(rng.integers(0, w)), int(rng.integers(0, h))
+                roi = (x0, y0, int(rng.integers(x0, w)), int(rng.integers(y0, h)))
+            rmin, rmax = (roi[:2], roi[2:]) if roi else (None, None)
+            for norm, trunc in ((True, True), (False, False), (True, False)):
+                got = make_signed_distance_field(mask, rmin, rmax, norm, trunc, 0.1,
+                                                 metric=SdfMetric.kL2)
+                want = port.make_sdf_l2(mask, roi, norm, trunc, 0.1)
+                assert bits_equal(got, want), (kind, t, norm, trunc, h, w, roi)
+    cam = S.circle_cameras(3, 1000)[1]
+    big = S.silhouette(cam, S.DUMBBELL)[:777, :]
+    assert bits_equal(make_signed_distance_field(big, use_truncation=True, metric=SdfMetric.kL2),
+                      port.make_sdf_l2(big, None, True, True, 0.1))
+    # end to end: carve with the option == oracle fusion fed with the Euclidean images
+    o = S.grid_option(40, weighted=True)
+    o.sdf_metric = SdfMetric.kL2
+    car = VoxelCarver(o)
+    assert car.Init()
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True)
+    orc = port.carver(opt)
+    for c in S.circle_cameras(7, 200, tilt=0.4):
+        m = S.silhouette(c, S.DUMBBELL)
+        ok, got = car.Carve(c, m, return_sdf=True)
+        want = port.make_sdf_l2(m, None, True, True, 0.1)
+        assert ok and bits_equal(got, want)
+        orc.carve_sdf(H.to_oracle_camera(c), want)
+    (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(car.ExtractIsoSurface(), orc.extract_iso(), o.bb_min, o.bb_max)

@@ -211,3 +211,41 @@ def test_sdf_color_map_vs_reference(ref, port, bunny):
         for lo, hi in ((-1.0, 1.0), (-0.3, 2.5)):
             assert np.array_equal(ref.signed_distance_to_color(img, lo, hi),
                                   port.signed_distance_to_color(img, lo, hi))
+
+
+def test_euclidean_sdf_oracle_vs_scipy_and_brute_force(port):
+    """The opt-in Euclidean metric has no counterpart in the reference; its checker is pinned against
+    scipy.ndimage.distance_transform_edt (full-image ROI) and an exhaustive search (ROI windows)."""
+    from scipy import ndimage
+    rng = np.random.default_rng(21)
+    for kind in ("blobs", "noise", "grey"):
+        for _ in range(6):
+            h, w = int(rng.integers(2, 70)), int(rng.integers(2, 70))
+            mask = H.random_mask(rng, h, w, kind)
+            fg = mask == 255
+            if fg.all() or not fg.any():
+                continue
+            want = np.where(fg, -ndimage.distance_transform_edt(fg),
+                            ndimage.distance_transform_edt(~fg)).astype(np.float32)
+            got = port.make_sdf_l2(mask, None, False, False, 0.1)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), kind
+    for _ in range(10):  # ROI windows, exhaustive
+        h, w = int(rng.integers(3, 24)), int(rng.integers(3, 24))
+        mask = H.random_mask(rng, h, w, "noise")
+        x0, y0 = int(rng.integers(0, w - 1)), int(rng.integers(0, h - 1))
+        x1, y1 = int(rng.integers(x0, w)), int(rng.integers(y0, h))
+        got = port.make_sdf_l2(mask, (x0, y0, x1, y1), False, False, 0.1)
+        want = np.zeros((h, w), np.float32)
+        ys, xs = np.mgrid[y0:y1 + 1, x0:x1 + 1]
+        fg = mask[y0:y1 + 1, x0:x1 + 1] == 255
+        for y in range(y0, y1 + 1):
+            for x in range(x0, x1 + 1):
+                me = mask[y, x] == 255
+                other = fg != me
+                if other.any():
+                    d2 = ((ys - y) ** 2 + (xs - x) ** 2)[other].min()
+                    e = np.float32(np.sqrt(np.float64(d2)))
+                else:
+                    e = np.finfo(np.float32).max
+                want[y, x] = -e if me else e
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))

@@ -7,7 +7,7 @@ Python hosts (tests, bench.py).  There is no CPU fallback: importing works anywh
 a carver without the built library or without a CUDA device raises.
 """
 from .capi import LibraryMissing, VcbError, load_library  # noqa: F401
-from .carver import (Camera, OrthoCamera, PinholeCamera, SdfInterpolation,  # noqa: F401
+from .carver import (Camera, OrthoCamera, PinholeCamera, SdfInterpolation, SdfMetric,  # noqa: F401
                      UpdateOutsideImage, VoxelCarver, VoxelCarverOption, VoxelUpdate,
                      VoxelUpdateOption, distance_transform_l1, make_signed_distance_field,
                      signed_distance_to_color, w2c_from_c2w)

@@ -6,6 +6,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("VACANCY_B200_LIB", os.path.join(HERE, "libvacancy_b200.so"))
 
 
+ABI_VERSION = 2  # VCB_ABI_VERSION of include/vacancy_b200.h
+
+
 class LibraryMissing(RuntimeError):
     pass
 
@@ -23,7 +26,8 @@ class Options(C.Structure):
                 ("sdf_interp", C.c_int32), ("update_outside", C.c_int32),
                 ("voxel_max_update_num", C.c_int32), ("voxel_update_weight", C.c_float),
                 ("use_truncation", C.c_int32), ("truncation_band", C.c_float),
-                ("device", C.c_int32), ("z_begin", C.c_int32), ("z_end", C.c_int32)]
+                ("device", C.c_int32), ("z_begin", C.c_int32), ("z_end", C.c_int32),
+                ("sdf_metric", C.c_int32)]
 
 
 class View(C.Structure):
@@ -34,11 +38,12 @@ class View(C.Structure):
 
 
 EXPORTS = [
-    "vcb_last_error", "vcb_invalid_sdf", "vcb_options_default", "vcb_create", "vcb_reset", "vcb_destroy",
+    "vcb_last_error", "vcb_abi_version", "vcb_invalid_sdf", "vcb_options_default", "vcb_create", "vcb_reset", "vcb_destroy",
     "vcb_grid_dims", "vcb_slab_range", "vcb_grid_positions", "vcb_set_stream", "vcb_synchronize",
     "vcb_flush", "vcb_carve_masks", "vcb_carve_masks_device", "vcb_carve_sdfs",
     "vcb_carve_sdfs_device", "vcb_distance_transform_l1", "vcb_make_signed_distance_field",
     "vcb_make_signed_distance_field_noalloc", "vcb_signed_distance_to_color",
+    "vcb_make_signed_distance_field_l2",
     "vcb_extract_iso_count", "vcb_extract_iso_fill", "vcb_extract_iso_device",
     "vcb_extract_iso_begin", "vcb_extract_iso_vertices", "vcb_extract_iso_export_top",
     "vcb_extract_iso_import_bottom", "vcb_extract_iso_faces", "vcb_halo_device",
@@ -64,6 +69,9 @@ def load_library(path=LIB_PATH):
     L.vcb_last_error.restype = C.c_char_p
     L.vcb_last_error.argtypes = [vp]
     L.vcb_invalid_sdf.restype = C.c_float
+    if L.vcb_abi_version() != ABI_VERSION:
+        raise LibraryMissing("%s has ABI version %d, this package expects %d: rebuild it"
+                             % (path, L.vcb_abi_version(), ABI_VERSION))
     L.vcb_options_default.argtypes = [C.POINTER(Options)]
     L.vcb_options_default.restype = None
     L.vcb_create.argtypes = [C.POINTER(Options), C.POINTER(vp)]
@@ -86,6 +94,8 @@ def load_library(path=LIB_PATH):
                                                  fp]
     L.vcb_make_signed_distance_field_noalloc.argtypes = [i32, vp, i32, i32, ip, ip, i32, i32,
                                                          C.c_float, vp, vp]
+    L.vcb_make_signed_distance_field_l2.argtypes = [i32, u8p, i32, i32, ip, ip, i32, i32, C.c_float,
+                                                    fp]
     L.vcb_signed_distance_to_color.argtypes = [i32, fp, i32, i32, C.c_float, C.c_float, u8p]
     L.vcb_extract_iso_count.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
     L.vcb_extract_iso_begin.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]

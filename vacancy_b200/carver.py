@@ -29,6 +29,13 @@ class UpdateOutsideImage(enum.IntEnum):  # voxel_carver.h:33-37
     kMax = 1
 
 
+class SdfMetric(enum.IntEnum):
+    """Metric of the 2D silhouette distance: kL1 is the reference's (voxel_carver.cc:102-167) and
+    the default; kL2 (exact Euclidean) is an addition of this library."""
+    kL1 = 0
+    kL2 = 1
+
+
 @dataclass
 class VoxelUpdateOption:  # voxel_carver.h:43-52
     voxel_update: VoxelUpdate = VoxelUpdate.kMax
@@ -47,6 +54,7 @@ class VoxelCarverOption:  # voxel_carver.h:54-60
     resolution: float = 0.1
     sdf_minmax_normalize: bool = True
     update_option: VoxelUpdateOption = field(default_factory=VoxelUpdateOption)
+    sdf_metric: SdfMetric = SdfMetric.kL1  # not in the reference; kL1 reproduces it
 
 
 def w2c_from_c2w(c2w):
@@ -174,6 +182,7 @@ def _fill_options(o, opt, device=0, z_range=None):
     o.use_truncation = int(bool(u.use_truncation))
     o.truncation_band = u.truncation_band
     o.device = int(device)
+    o.sdf_metric = int(getattr(opt, "sdf_metric", 0))
     if z_range is not None:
         o.z_begin, o.z_end = int(z_range[0]), int(z_range[1])
 
@@ -383,15 +392,19 @@ def distance_transform_l1(mask, roi_min=None, roi_max=None, device=0):
 
 
 def make_signed_distance_field(mask, roi_min=None, roi_max=None, minmax_normalize=True,
-                               use_truncation=False, truncation_band=0.1, device=0):
-    """MakeSignedDistanceField (voxel_carver.h:122-126) on the GPU."""
+                               use_truncation=False, truncation_band=0.1, device=0,
+                               metric=SdfMetric.kL1):
+    """MakeSignedDistanceField (voxel_carver.h:122-126) on the GPU; metric=kL2 selects the exact
+    Euclidean variant (no reference counterpart)."""
     L = capi.load_library()
     mask = np.ascontiguousarray(mask, np.uint8)
     h, w = mask.shape
     rmin = (C.c_int32 * 2)(*(roi_min if roi_min is not None else (0, 0)))
     rmax = (C.c_int32 * 2)(*(roi_max if roi_max is not None else (w - 1, h - 1)))
     out = np.empty((h, w), np.float32)
-    capi.check(L, None, L.vcb_make_signed_distance_field(
+    fn = (L.vcb_make_signed_distance_field_l2 if int(metric) == int(SdfMetric.kL2)
+          else L.vcb_make_signed_distance_field)
+    capi.check(L, None, fn(
         device, mask.ctypes.data_as(C.POINTER(C.c_uint8)), w, h, rmin, rmax,
         int(minmax_normalize), int(use_truncation), C.c_float(truncation_band),
         out.ctypes.data_as(C.POINTER(C.c_float))))

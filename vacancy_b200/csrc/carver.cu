@@ -176,6 +176,8 @@ int validate(const vcb_options* o, int dims[3]) {
     return fail(nullptr, VCB_ERR_INVALID, "unknown sdf_interp %d", o->sdf_interp);
   if (o->update_outside != VCB_OUTSIDE_NONE && o->update_outside != VCB_OUTSIDE_MAX)
     return fail(nullptr, VCB_ERR_INVALID, "unknown update_outside %d", o->update_outside);
+  if (o->sdf_metric != VCB_METRIC_L1 && o->sdf_metric != VCB_METRIC_L2)
+    return fail(nullptr, VCB_ERR_INVALID, "unknown sdf_metric %d", o->sdf_metric);
   for (int i = 0; i < 3; i++) {
     const float diff = o->bb_max[i] - o->bb_min[i];
     const float q = diff / o->resolution;  // voxel_carver.cc:294-296 (truncating cast)
@@ -379,7 +381,9 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
     if ((rc = check_view(c, views[i])) != VCB_OK) return rc;
     if (!masks[i]) return fail(c, VCB_ERR_INVALID, "mask %d is null", i);
     max_pix = max(max_pix, (size_t)views[i].width * views[i].height);
-    max_scr = max(max_scr, sdf_scratch_bytes(views[i].width, views[i].height));
+    max_scr = max(max_scr, sdf_scratch_bytes(views[i].width, views[i].height,
+                                             c->opt.sdf_metric == VCB_METRIC_L2 ? kSdfSignedL2
+                                                                                : kSdfSigned));
   }
   if (n_views == 0) return VCB_OK;
   if ((rc = ensure_pool(c, max_pix)) != VCB_OK) return rc;
@@ -441,7 +445,8 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
     }
     {
       Span span(c, 0);
-      launch_sdf2d(hv, nb, kSdfSigned, c->opt.sdf_minmax_normalize, c->opt.use_truncation,
+      launch_sdf2d(hv, nb, c->opt.sdf_metric == VCB_METRIC_L2 ? kSdfSignedL2 : kSdfSigned,
+                   c->opt.sdf_minmax_normalize, c->opt.use_truncation,
                    c->opt.truncation_band, c->stream, &c->stage_launches[0]);
     }
     CU(c, cudaGetLastError());
@@ -489,6 +494,8 @@ void set_global_error(const char* text) { g_last_error = text; }
 extern "C" {
 
 const char* vcb_last_error(const vcb_carver* c) { return c ? c->err.c_str() : g_last_error.c_str(); }
+
+int vcb_abi_version(void) { return VCB_ABI_VERSION; }
 
 float vcb_invalid_sdf(void) { return kInvalidSdf; }
 
@@ -805,7 +812,7 @@ static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width,
   Scratch buf;
   // layout: float out | kernel scratch | mask | SdfView | int absmax | float max
   const size_t off_scr = (pix * sizeof(float) + 255) & ~(size_t)255;
-  const size_t off_mask = off_scr + sdf_scratch_bytes(width, height);
+  const size_t off_mask = off_scr + sdf_scratch_bytes(width, height, mode);
   const size_t off_view = (off_mask + pix + 255) / 256 * 256;
   const size_t off_misc = off_view + 256;
   CU(nullptr, buf.reserve(off_misc + 256));
@@ -870,6 +877,14 @@ int vcb_make_signed_distance_field(int32_t device, const uint8_t* mask, int32_t 
                                    const int32_t roi_max[2], int32_t minmax_normalize,
                                    int32_t use_truncation, float truncation_band, float* dist) {
   return sdf_free_function(device, mask, width, height, roi_min, roi_max, kSdfSigned,
+                           minmax_normalize, use_truncation, truncation_band, dist);
+}
+
+int vcb_make_signed_distance_field_l2(int32_t device, const uint8_t* mask, int32_t width,
+                                      int32_t height, const int32_t roi_min[2],
+                                      const int32_t roi_max[2], int32_t minmax_normalize,
+                                      int32_t use_truncation, float truncation_band, float* dist) {
+  return sdf_free_function(device, mask, width, height, roi_min, roi_max, kSdfSignedL2,
                            minmax_normalize, use_truncation, truncation_band, dist);
 }
 

@@ -82,9 +82,12 @@ struct SdfView {
   int rx0, ry0, rx1, ry1;
 };
 
-enum SdfMode { kSdfSigned = 0, kSdfDistanceL1 = 1 };
+// kSdfSigned: MakeSignedDistanceField (L1, the reference); kSdfDistanceL1: DistanceTransformL1;
+// kSdfSignedL2: the same signed field with the exact Euclidean metric (no reference counterpart)
+enum SdfMode { kSdfSigned = 0, kSdfDistanceL1 = 1, kSdfSignedL2 = 2 };
 
-size_t sdf_scratch_bytes(int width, int height);  // per-view scratch of the 2D SDF kernels
+// per-view scratch of the 2D SDF kernels (the Euclidean mode needs three more int32 planes)
+size_t sdf_scratch_bytes(int width, int height, int mode = kSdfSigned);
 
 // up to kSdfSubBatch view descriptors, passed to the kernels by value (kernel parameter bank)
 struct SdfBatch {

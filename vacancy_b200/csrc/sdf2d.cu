@@ -35,9 +35,13 @@ __host__ __device__ inline int sdf_pitch(int width) { return (width + 31) & ~31;
 __host__ __device__ inline size_t sdf_plane_bytes(int width, int height) {
   return ((size_t)sdf_pitch(width) * height * sizeof(int16_t) + 255) & ~(size_t)255;
 }
-size_t sdf_scratch_bytes(int width, int height) {
-  const size_t bits = ((size_t)(sdf_pitch(width) / 32) * height * sizeof(uint32_t) + 255) & ~(size_t)255;
-  return 2 * sdf_plane_bytes(width, height) + bits;
+__host__ __device__ inline size_t sdf_bits_bytes(int width, int height) {
+  return ((size_t)(sdf_pitch(width) / 32) * height * sizeof(uint32_t) + 255) & ~(size_t)255;
+}
+size_t sdf_scratch_bytes(int width, int height, int mode) {
+  const size_t base = 2 * sdf_plane_bytes(width, height) + sdf_bits_bytes(width, height);
+  // Euclidean mode: parabola stack (two int32 planes) + squared distances (one int32 plane)
+  return mode == kSdfSignedL2 ? base + 6 * sdf_plane_bytes(width, height) : base;
 }
 
 namespace {
@@ -50,6 +54,12 @@ __device__ __forceinline__ int16_t* view_cold(const SdfView& v) {
 }
 __device__ __forceinline__ uint32_t* view_bits(const SdfView& v) {
   return reinterpret_cast<uint32_t*>(v.scratch + 2 * sdf_plane_bytes(v.width, v.height));
+}
+// int32 planes of the Euclidean mode: 0 = stack of parabolas, 1 = their start rows, 2 = result
+__device__ __forceinline__ int32_t* view_l2_plane(const SdfView& v, int k) {
+  return reinterpret_cast<int32_t*>(v.scratch + 2 * sdf_plane_bytes(v.width, v.height) +
+                                    sdf_bits_bytes(v.width, v.height) +
+                                    (size_t)k * 2 * sdf_plane_bytes(v.width, v.height));
 }
 
 __device__ __forceinline__ float atomic_max_float(float* addr, float value) {
@@ -379,6 +389,72 @@ __global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const __grid_constan
   if (cx == 0 && local_max > 0) atomicMax(v.absmax, local_max);
 }
 
+// ---- pass 2 (Euclidean mode): exact squared distance along the column --------------------------
+// No counterpart in the reference (its transform is the L1 one above); offered because hosts may
+// want the true Euclidean silhouette distance.  D2(x, y) = min over y' of (y - y')^2 + g(x, y')^2
+// with g the row distance (0 on pixels of the other class): the lower envelope of parabolas, built
+// with integer arithmetic only (Meijster, Roerdink, Hesselink 2000, phase 2), one thread per column,
+// once per polarity.  The stack lives in global memory (coalesced across the columns of a warp).
+__global__ void __launch_bounds__(128) sdf_col_l2_kernel(const __grid_constant__ SdfBatch B) {
+  const SdfView& v = B.v[blockIdx.y];
+  const int x = v.rx0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int local_max = 0;
+  if (x <= v.rx1) {
+    const int pitch = sdf_pitch(v.width);
+    const int m = v.ry1 - v.ry0 + 1;
+    const int16_t* __restrict__ rowd = view_rowd(v) + (size_t)v.ry0 * pitch + x;
+    int32_t* __restrict__ st = view_l2_plane(v, 0) + x;  // (g << 16) | row of each parabola
+    int32_t* __restrict__ tt = view_l2_plane(v, 1) + x;  // first row where it is the lowest
+    int32_t* __restrict__ out = view_l2_plane(v, 2) + (size_t)v.ry0 * pitch + x;
+    for (int pol = 0; pol < 2; pol++) {  // 0: distance to background (for foreground pixels)
+      int q = -1;
+      for (int u = 0; u < m; u++) {
+        const int r = __ldg(rowd + (size_t)u * pitch);
+        const int gu = pol == 0 ? max(-r, 0) : max(r, 0);
+        if (gu >= kRowInf) continue;  // no pixel of the other class in this row
+        while (q >= 0) {
+          const int e = st[(size_t)q * pitch], i = e & 0xffff, gi = e >> 16, tq = tt[(size_t)q * pitch];
+          if ((tq - i) * (tq - i) + gi * gi > (tq - u) * (tq - u) + gu * gu) {
+            q--;
+          } else {
+            break;
+          }
+        }
+        if (q < 0) {
+          q = 0;
+          st[0] = (gu << 16) | u;
+          tt[0] = 0;
+        } else {
+          const int e = st[(size_t)q * pitch], i = e & 0xffff, gi = e >> 16;
+          const long long num = (long long)u * u - (long long)i * i + (long long)gu * gu -
+                                (long long)gi * gi;
+          const int w = 1 + (int)(num / (2 * (u - i)));
+          if (w < m) {
+            q++;
+            st[(size_t)q * pitch] = (gu << 16) | u;
+            tt[(size_t)q * pitch] = w;
+          }
+        }
+      }
+      for (int u = m - 1; u >= 0; u--) {
+        const int r = __ldg(rowd + (size_t)u * pitch);
+        int d2 = INT_MAX;  // no seed in the whole column range: "infinitely far"
+        if (q >= 0) {
+          const int e = st[(size_t)q * pitch], i = e & 0xffff, gi = e >> 16;
+          d2 = (u - i) * (u - i) + gi * gi;
+          if (u == tt[(size_t)q * pitch]) q--;
+        }
+        if ((pol == 0) == (r < 0)) {  // this pixel belongs to the polarity being resolved
+          out[(size_t)u * pitch] = r < 0 ? -d2 : d2;
+          local_max = max(local_max, d2);
+        }
+      }
+    }
+  }
+  local_max = __reduce_max_sync(0xffffffffu, local_max);
+  if ((threadIdx.x & 31) == 0 && local_max > 0) atomicMax(v.absmax, local_max);
+}
+
 // ---- pass 3: int -> float, normalisation, truncation, image maximum, 8x8-block flags. -----------
 // One block per band of 8 image rows, one thread per 8x8-pixel block of the band: 16-byte loads of
 // the int16 distances, 16-byte stores of the floats (when the width allows), and - because a thread
@@ -387,8 +463,14 @@ __global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const __grid_constan
 __device__ __forceinline__ float sdf_value(int d, int mode, bool do_norm, float norm, int truncate,
                                            float band) {
   float f;
-  if (mode == kSdfSigned) {
-    f = d == kRowInf ? FLT_MAX : (d == -kRowInf ? -FLT_MAX : (float)d);
+  if (mode == kSdfSigned || mode == kSdfSignedL2) {
+    if (mode == kSdfSigned) {
+      f = d == kRowInf ? FLT_MAX : (d == -kRowInf ? -FLT_MAX : (float)d);
+    } else {  // d = signed squared distance; the distance is the double square root rounded to float
+      const int a = d < 0 ? -d : d;
+      const float e = a == INT_MAX ? FLT_MAX : (float)__dsqrt_rn((double)a);
+      f = d < 0 ? -e : e;
+    }
     if (do_norm) f = __fmul_rn(f, norm);
     if (truncate) {  // voxel_carver.cc:225-236
       if (-band >= f) {
@@ -412,9 +494,11 @@ __global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant
   if (y0 >= v.height) return;
   float norm = 1.0f;
   bool do_norm = false;
-  if (normalize && mode == kSdfSigned) {
+  if (normalize && (mode == kSdfSigned || mode == kSdfSignedL2)) {
     const int am_i = *v.absmax;
-    const float am = am_i == INT_MAX ? FLT_MAX : (float)am_i;
+    const float am = am_i == INT_MAX
+                         ? FLT_MAX
+                         : (mode == kSdfSignedL2 ? (float)__dsqrt_rn((double)am_i) : (float)am_i);
     if (am > FLT_MIN) {  // voxel_carver.cc:213
       do_norm = true;
       norm = __fdiv_rn(1.0f, am);
@@ -422,6 +506,7 @@ __global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant
   }
   const int pitch = sdf_pitch(v.width);
   const int16_t* __restrict__ cold = view_cold(v);
+  const int32_t* __restrict__ d2p = mode == kSdfSignedL2 ? view_l2_plane(v, 2) : nullptr;
   const int nbx = (v.width + kTilePx - 1) / kTilePx;
   const int words = (nbx + 31) / 32;
   const bool vec_out = (v.width & 3) == 0;
@@ -439,13 +524,27 @@ __global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant
         const bool row_in = y >= v.ry0 && y <= v.ry1;
         float f[kTilePx];
         // the int16 scratch rows are padded to 32 pixels: the 16-byte load is always in bounds
-        const uint4 raw = row_in ? __ldg(reinterpret_cast<const uint4*>(cold + (size_t)y * pitch + x0))
-                                 : make_uint4(0, 0, 0, 0);
-        const unsigned rw[4] = {raw.x, raw.y, raw.z, raw.w};
+        int dd[kTilePx];
+        if (mode == kSdfSignedL2) {
+          const int4* __restrict__ p = reinterpret_cast<const int4*>(d2p + (size_t)y * pitch + x0);
+          const int4 lo = row_in ? __ldg(p) : make_int4(0, 0, 0, 0);
+          const int4 hi = row_in ? __ldg(p + 1) : make_int4(0, 0, 0, 0);
+          dd[0] = lo.x; dd[1] = lo.y; dd[2] = lo.z; dd[3] = lo.w;
+          dd[4] = hi.x; dd[5] = hi.y; dd[6] = hi.z; dd[7] = hi.w;
+        } else {
+          const uint4 raw = row_in
+                                ? __ldg(reinterpret_cast<const uint4*>(cold + (size_t)y * pitch + x0))
+                                : make_uint4(0, 0, 0, 0);
+          const unsigned rw[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+          for (int i = 0; i < kTilePx; i++) {
+            dd[i] = (int)(int16_t)((rw[i >> 1] >> (16 * (i & 1))) & 0xffffu);
+          }
+        }
 #pragma unroll
         for (int i = 0; i < kTilePx; i++) {
           const int x = x0 + i;
-          const int d = (int)(int16_t)((rw[i >> 1] >> (16 * (i & 1))) & 0xffffu);
+          const int d = dd[i];
           // zeros outside the ROI, voxel_carver.cc:104
           f[i] = (row_in && x >= v.rx0 && x <= v.rx1)
                      ? sdf_value(d, mode, do_norm, norm, truncate, band)
@@ -544,7 +643,9 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
   sdf_row_kernel<<<dim3((max_rows + kRowWarps - 1) / kRowWarps, n_views), kRowWarps * 32, 0,
                    stream>>>(views_dev);
   const int max_seglen = (max_rows + 31) / 32;
-  if (max_seglen <= kColMaxSegLen) {
+  if (mode == kSdfSignedL2) {
+    sdf_col_l2_kernel<<<dim3((max_cols + 127) / 128, n_views), 128, 0, stream>>>(views_dev);
+  } else if (max_seglen <= kColMaxSegLen) {
     const size_t smem = (size_t)32 * 32 * max_seglen * sizeof(int16_t);
     static bool attr_set[64] = {false};
     int dev = 0;

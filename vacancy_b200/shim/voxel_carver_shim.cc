@@ -194,6 +194,11 @@ void VoxelCarver::set_option(VoxelCarverOption option) { option_ = option; }
 
 bool VoxelCarver::Init() {  // voxel_carver.cc:375-392; calling it again re-creates the grid
   drop_carver(this);
+  if (vcb_abi_version() != VCB_ABI_VERSION) {
+    LOGE("VoxelCarver::Init libvacancy_b200.so has ABI %d, this shim was built for %d\n",
+         vcb_abi_version(), VCB_ABI_VERSION);
+    return false;
+  }
   vcb_options o;
   vcb_options_default(&o);
   for (int a = 0; a < 3; a++) {
