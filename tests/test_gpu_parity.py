@@ -427,3 +427,43 @@ def test_euclidean_metric_option(cuda_lib, port):
     (gs, gn), (ws, wn) = car.download_grid(), orc.download()
     assert np.array_equal(gn, wn) and bits_equal(gs, ws)
     H.assert_mesh_equal(car.ExtractIsoSurface(), orc.extract_iso(), o.bb_min, o.bb_max)
+
+
+def test_random_cameras_fuzz(cuda_lib, port):
+    """Random poses (any roll, cameras inside / outside the box, some behind it), fx != fy, ROI
+    sub-windows, both update modes: exercises the tile classification, the shared-reciprocal
+    projection and the fallback paths against the oracle, bit for bit."""
+    rng = np.random.default_rng(2024)
+    for trial in range(10):
+        n = int(rng.choice([24, 40, 56]))
+        weighted = bool(trial % 2)
+        o = S.grid_option(n, weighted=weighted, band=float(rng.choice([0.05, 0.1, 0.3])))
+        opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=int(weighted),
+                             truncation=weighted, band=o.update_option.truncation_band,
+                             outside=int(trial % 5 == 4))
+        car, orc = make_carver(opt), port.carver(opt)
+        size = int(rng.choice([96, 160, 256]))
+        for v in range(6):
+            pos = rng.normal(size=3)
+            pos *= rng.uniform(0.2, 4.0) / np.linalg.norm(pos)
+            target = rng.uniform(-0.3, 0.3, 3)
+            up = rng.normal(size=3)
+            c2w = S.look_at_c2w(pos, target, up)
+            fx, fy = rng.uniform(0.5, 2.0, 2) * size
+            cx, cy = size / 2 + rng.uniform(-20, 20, 2)
+            ocam = B.Camera(size, size, c2w, fx, fy, cx, cy)
+            pcam = H.product_camera(ocam)
+            ref_cam = S.PinholeCamera(size, size, c2w, (cx, cy), (fx, fy))
+            mask = S.silhouette(ref_cam, S.DUMBBELL)
+            roi = None
+            if v % 3 == 2:
+                roi = (int(rng.integers(0, 20)), int(rng.integers(0, 20)),
+                       size - 1 - int(rng.integers(0, 20)), size - 1 - int(rng.integers(0, 20)))
+            kw = dict(roi_min=roi[:2], roi_max=roi[2:]) if roi else {}
+            ok, got = car.Carve(pcam, mask, return_sdf=True, **kw)
+            want = orc.carve_mask(ocam, mask, roi)
+            assert ok and bits_equal(got, want), (trial, v)
+        (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+        assert np.array_equal(gn, wn), trial
+        assert bits_equal(gs, ws), trial
+        H.assert_mesh_equal(car.ExtractIsoSurface(), orc.extract_iso(), o.bb_min, o.bb_max)
