@@ -1,10 +1,12 @@
 // K2 - ExtractVoxel on the GPU, plus the device-wide scan shared with marching cubes.
 //
 // Replaces vacancy::ExtractVoxel (extract_voxel.cc:258-317) and UpdateOnSurface (:15-79).
-//   voxel_flag_kernel : one warp per 32-voxel segment along x; the emit predicate of :279-289
-//                       (or the on_surface rule of :26-77) -> ballot word + popcount per segment.
-//   scan_exclusive_u64: 3-kernel exclusive prefix sum over the per-segment counts; segments are
-//                       in raster order (x fastest), so the prefix IS the reference's emission order.
+//   voxel_flag_kernel : block per 2 grid rows, 8 coalesced loads in flight per thread; the emit
+//                       predicate of :279-289 (or the on_surface rule of :26-77) -> one ballot word
+//                       per 32 voxels + one count per row.
+//   scan_exclusive_u64: 3-kernel exclusive prefix sum over the per-ROW counts; rows are in raster
+//                       order and a warp sums the popcounts before its segment, so numbering IS the
+//                       reference's emission order.
 //   voxel_emit_kernel : every flagged voxel becomes MakeCube(resolution) (mesh.cc:728-780) moved to
 //                       the voxel centre: 24 vertices + 12 faces, written cooperatively by the warp.
 // HBM-bound: 8 B/voxel read (sdf + update_num) + 432 B per emitted voxel written.
@@ -152,50 +154,96 @@ __host__ __device__ inline SegGeom seg_geom(const GridDesc& g) {
   return s;
 }
 
+// One block per kFlagRows grid rows; a warp iteration covers 128 voxels of each row with four
+// coalesced loads of sdf and of update_num per row, evaluates the emit predicate, and turns every
+// 32 voxels into one bitmap word with a ballot; each row's count is the sum of its popcounts.
+constexpr int kFlagRows = 2;
+
+__device__ __forceinline__ bool emit_predicate(const GridDesc& g, int inside_empty, float s, int n,
+                                               size_t id, int x, int y, int zl) {
+  if (!inside_empty) return !(s > 0.0f || n < 1);  // extract_voxel.cc:285
+  if (n < 1) return false;                         // extract_voxel.cc:26-77
+  const size_t plane = (size_t)g.nx * g.ny;
+  const bool tiny = fabsf(s) < FLT_MIN;
+  bool emit = false;
+  if (x >= 1 && g.update_num[id - 1] >= 1) emit |= (__fmul_rn(s, g.sdf[id - 1]) < 0.0f) || tiny;
+  if (y >= 1 && g.update_num[id - g.nx] >= 1) emit |= (__fmul_rn(s, g.sdf[id - g.nx]) < 0.0f) || tiny;
+  if (zl >= 1 && g.update_num[id - plane] >= 1) emit |= (__fmul_rn(s, g.sdf[id - plane]) < 0.0f) || tiny;
+  return emit;
+}
+
 __global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int inside_empty,
                                                          uint32_t* __restrict__ bits,
-                                                         uint64_t* __restrict__ segcnt) {
+                                                         uint64_t* __restrict__ rowcnt) {
   const SegGeom sg = seg_geom(g);
-  const int lane = threadIdx.x & 31;
-  const int64_t seg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (seg >= sg.n_segs) return;
-  const int sx = (int)(seg % sg.segs_per_row);
-  const int64_t row = seg / sg.segs_per_row;
-  const int y = (int)(row % g.ny);
-  const int zl = (int)(row / g.ny);  // local plane
-  const int x = sx * kSegVoxels + lane;
-  bool emit = false;
-  if (x < g.nx) {
-    const size_t plane = (size_t)g.nx * g.ny;
-    const size_t id = (size_t)zl * plane + (size_t)y * g.nx + x;
-    const float s = g.sdf[id];
-    const int n = g.update_num[id];
-    if (!inside_empty) {
-      emit = !(s > 0.0f || n < 1);  // extract_voxel.cc:285
-    } else if (n >= 1) {            // extract_voxel.cc:26-77
-      const bool tiny = fabsf(s) < FLT_MIN;
-      // previous voxel along x, y, z; the z neighbour of the first owned plane is the halo plane
-      if (x >= 1 && g.update_num[id - 1] >= 1) {
-        emit |= (__fmul_rn(s, g.sdf[id - 1]) < 0.0f) || tiny;
-      }
-      if (y >= 1 && g.update_num[id - g.nx] >= 1) {
-        emit |= (__fmul_rn(s, g.sdf[id - g.nx]) < 0.0f) || tiny;
-      }
-      if (zl >= 1 && g.update_num[id - plane] >= 1) {
-        emit |= (__fmul_rn(s, g.sdf[id - plane]) < 0.0f) || tiny;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  const int64_t n_rows = (int64_t)g.ny * (g.z_end - g.z_begin);
+  const int64_t row0 = (int64_t)blockIdx.x * kFlagRows;
+  const int groups = (sg.segs_per_row + 3) / 4;
+  __shared__ unsigned s_cnt[kFlagRows];
+  if (threadIdx.x < kFlagRows) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  unsigned cnt[kFlagRows];
+#pragma unroll
+  for (int r = 0; r < kFlagRows; r++) cnt[r] = 0;
+  for (int c = warp; c < groups; c += warps) {
+    const int x = c * 128 + lane;
+    float s[kFlagRows][4];
+    int n[kFlagRows][4];
+#pragma unroll
+    for (int r = 0; r < kFlagRows; r++) {
+      const bool row_ok = row0 + r < n_rows;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const bool ok = row_ok && x + 32 * q < g.nx;
+        const size_t id = (size_t)(row0 + r) * g.nx + x + 32 * q;
+        s[r][q] = ok ? g.sdf[id] : 1.0f;
+        n[r][q] = ok ? g.update_num[id] : 0;
       }
     }
+#pragma unroll
+    for (int r = 0; r < kFlagRows; r++) {
+      const int64_t row = row0 + r;
+      const int y = (int)(row % g.ny), zl = (int)(row / g.ny);
+      unsigned word = 0;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int xx = x + 32 * q;
+        const bool ok = row < n_rows && xx < g.nx;
+        const bool emit = ok && emit_predicate(g, inside_empty, s[r][q], n[r][q],
+                                               (size_t)row * g.nx + xx, xx, y, zl);
+        const unsigned w_q = __ballot_sync(0xffffffffu, emit);
+        if (lane == q) word = w_q;
+        cnt[r] += lane == 0 ? __popc(w_q) : 0;
+      }
+      const int w = c * 4 + lane;
+      if (lane < 4 && row < n_rows && w < sg.segs_per_row) bits[row * sg.segs_per_row + w] = word;
+    }
   }
-  const unsigned word = __ballot_sync(0xffffffffu, emit);
-  if (lane == 0) {
-    bits[seg] = word;
-    segcnt[seg] = (uint64_t)__popc(word);
+#pragma unroll
+  for (int r = 0; r < kFlagRows; r++) {
+    if (lane == 0 && cnt[r]) atomicAdd(&s_cnt[r], cnt[r]);
   }
+  __syncthreads();
+  if (threadIdx.x < kFlagRows && row0 + threadIdx.x < n_rows) {
+    rowcnt[row0 + threadIdx.x] = s_cnt[threadIdx.x];
+  }
+}
+
+// number of flagged voxels of the row before segment `sx` (sum of popcounts, by one warp)
+__device__ __forceinline__ unsigned row_prefix(const uint32_t* __restrict__ row_bits, int sx,
+                                               int lane) {
+  unsigned c = 0;
+  for (int s0 = 0; s0 < sx; s0 += 32) {
+    const int i = s0 + lane;
+    c += i < sx ? __popc(row_bits[i]) : 0;
+  }
+  return __reduce_add_sync(0xffffffffu, c);
 }
 
 __global__ void __launch_bounds__(256) voxel_emit_kernel(const GridDesc g,
                                                          const uint32_t* __restrict__ bits,
-                                                         const uint64_t* __restrict__ segbase,
+                                                         const uint64_t* __restrict__ rowbase,
                                                          int64_t first, int64_t count,
                                                          float* __restrict__ vertices,
                                                          int32_t* __restrict__ faces) {
@@ -205,10 +253,11 @@ __global__ void __launch_bounds__(256) voxel_emit_kernel(const GridDesc g,
   if (seg >= sg.n_segs) return;
   unsigned word = bits[seg];
   if (word == 0) return;
-  int64_t k = (int64_t)segbase[seg];  // global cube number of the first flagged voxel
-  if (k >= first + count || k + __popc(word) <= first) return;
   const int sx = (int)(seg % sg.segs_per_row);
   const int64_t row = seg / sg.segs_per_row;
+  // global cube number of the segment's first flagged voxel
+  int64_t k = (int64_t)rowbase[row] + row_prefix(bits + row * sg.segs_per_row, sx, lane);
+  if (k >= first + count || k + __popc(word) <= first) return;
   const int y = (int)(row % g.ny);
   const int z = (int)(row / g.ny) + g.z_begin;
   const float h = g.resolution / 2;  // mesh.cc:736-738
@@ -251,23 +300,22 @@ cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, VoxelExtrac
   const SegGeom sg = seg_geom(g);
   st->n_voxels = -1;
   st->inside_empty = inside_empty;
+  if (inside_empty && g.z_begin > 0) return cudaErrorNotSupported;  // needs the plane below
+  const int64_t n_rows = (int64_t)g.ny * (g.z_end - g.z_begin);
   cudaError_t e;
   if ((e = st->bits.reserve((size_t)sg.n_segs * sizeof(uint32_t))) != cudaSuccess) return e;
-  // segbase holds n_segs prefixes followed by the total
-  if ((e = st->segbase.reserve((size_t)(sg.n_segs + 1) * sizeof(uint64_t))) != cudaSuccess) return e;
+  // per grid row: [0, n_rows) counts, [n_rows, 2 n_rows) exclusive prefix, then the total
+  if ((e = st->segbase.reserve((size_t)(2 * n_rows + 1) * sizeof(uint64_t))) != cudaSuccess) return e;
   uint32_t* bits = static_cast<uint32_t*>(st->bits.ptr);
-  uint64_t* segbase = static_cast<uint64_t*>(st->segbase.ptr);
-  GridDesc gd = g;
-  if (inside_empty && g.halo == 0 && g.z_begin > 0) return cudaErrorInvalidValue;
-  const int64_t threads = sg.n_segs * 32;
-  const unsigned blocks = (unsigned)((threads + 255) / 256);
-  voxel_flag_kernel<<<blocks, 256, 0, stream>>>(gd, inside_empty, bits, segbase);
+  uint64_t* rowcnt = static_cast<uint64_t*>(st->segbase.ptr);
+  uint64_t* rowbase = rowcnt + n_rows;
+  voxel_flag_kernel<<<(unsigned)((n_rows + kFlagRows - 1) / kFlagRows), 256, 0, stream>>>(
+      g, inside_empty, bits, rowcnt);
   if (launches) *launches += 1;
-  e = scan_exclusive_u64(segbase, segbase, sg.n_segs, segbase + sg.n_segs, &st->tmp, stream,
-                         launches);
+  e = scan_exclusive_u64(rowcnt, rowbase, n_rows, rowbase + n_rows, &st->tmp, stream, launches);
   if (e != cudaSuccess) return e;
   uint64_t total = 0;
-  e = cudaMemcpyAsync(&total, segbase + sg.n_segs, sizeof(total), cudaMemcpyDeviceToHost, stream);
+  e = cudaMemcpyAsync(&total, rowbase + n_rows, sizeof(total), cudaMemcpyDeviceToHost, stream);
   if (e != cudaSuccess) return e;
   if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return e;
   st->n_voxels = (int64_t)total;
@@ -286,9 +334,10 @@ cudaError_t voxel_extract_fill(const GridDesc& g, VoxelExtract* st, float* verti
   const unsigned blocks = (unsigned)((threads + 255) / 256);
   for (int64_t first = 0; first < st->n_voxels; first += chunk) {
     const int64_t count = st->n_voxels - first < chunk ? st->n_voxels - first : chunk;
-    voxel_emit_kernel<<<blocks, 256, 0, stream>>>(g, static_cast<uint32_t*>(st->bits.ptr),
-                                                  static_cast<uint64_t*>(st->segbase.ptr), first,
-                                                  count, dv, df);
+    voxel_emit_kernel<<<blocks, 256, 0, stream>>>(
+        g, static_cast<uint32_t*>(st->bits.ptr),
+        static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin), first,
+        count, dv, df);
     if (launches) *launches += 1;
     e = cudaMemcpyAsync(vertices_host + first * 72, dv, (size_t)count * 72 * sizeof(float),
                         cudaMemcpyDeviceToHost, stream);
