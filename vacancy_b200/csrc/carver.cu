@@ -70,6 +70,7 @@ struct vcb_carver {
   Scratch pool;          // kMaxViewsPerLaunch image slots
   size_t slot_floats = 0;
   Scratch max_sdf;       // one float per slot
+  Scratch fuse_tabs;     // per-launch tables of the fusion kernel (fusion_table_bytes)
   Scratch tiles;         // 8x8-block flags per slot (tile_flag_bytes), see fusion.cu
   size_t tile_slot_bytes = 0;
   bool use_tiles = true;
@@ -330,6 +331,13 @@ int flush_pending(vcb_carver* c) {
     const int64_t cap = (int64_t)c->opt.voxel_max_update_num + 1;
     const int rc = ensure_wtab(c, (c->max_count < cap ? c->max_count : cap) + 2);
     if (rc != VCB_OK) return rc;
+  }
+  {
+    const int64_t cap = (int64_t)c->opt.voxel_max_update_num + 1;
+    const int64_t fill = (c->max_count < cap ? c->max_count : cap) + 2;
+    c->fp.wtab_fill = (int)(fill < c->wtab_n ? fill : c->wtab_n);
+    CU(c, c->fuse_tabs.reserve(fusion_table_bytes(c->nx, c->ny, c->z_end - c->z_begin)));
+    c->fp.tables = static_cast<unsigned char*>(c->fuse_tabs.ptr);
   }
   c->fp.n_views = c->pending;
   // update_num <= views applied so far, so the `update_num > max` gate cannot fire before that
@@ -627,7 +635,7 @@ void vcb_destroy(vcb_carver* c) {
   cudaFree(c->pos_y);
   cudaFree(c->pos_z);
   cudaFree(c->wtab);
-  Scratch* all[] = {&c->pool, &c->max_sdf, &c->tiles, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
+  Scratch* all[] = {&c->pool, &c->max_sdf, &c->tiles, &c->fuse_tabs, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
                     &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo};

@@ -59,6 +59,7 @@ struct FuseParams {
   const float* pos_z;
   const float2* wtab;    // weighted-average table: {w*float(n), 1/(w*float(n+1))}, n in [0, wtab_n)
   int wtab_n;
+  int wtab_fill;         // entries a voxel can index during this launch (<= wtab_n)
   int nx, ny;
   int z_begin, z_end;    // owned planes
   int n_views;
@@ -67,8 +68,16 @@ struct FuseParams {
   int use_truncation;
   int update_outside;
   float weight;
+  float neg_zero;        // -0.0f, set by launch_fusion (an addend the compiler cannot fold, see fusion.cu)
+  // per-launch tables: `tables` is a device block of fusion_table_bytes() the caller provides,
+  // launch_fusion fills it (prep kernels) and sets the three pointers into it
+  unsigned char* tables;
+  const float4* view_tab;
+  const float4* mz_tab;
+  const unsigned char* tile_class;  // [fusion block][view], nullptr = every tile is "mixed"
   FuseView views[kMaxViewsPerLaunch];
 };
+size_t fusion_table_bytes(int nx, int ny, int nz_slab);
 
 // ---- per-view descriptor of the 2D SDF kernels (device array) ----
 struct SdfView {
