@@ -467,3 +467,45 @@ def test_random_cameras_fuzz(cuda_lib, port):
         assert np.array_equal(gn, wn), trial
         assert bits_equal(gs, ws), trial
         H.assert_mesh_equal(car.ExtractIsoSurface(), orc.extract_iso(), o.bb_min, o.bb_max)
+
+
+def test_long_weight_table_beyond_shared_copy(cuda_lib, port):
+    """700 weighted views with voxel_max_update_num = 5000: update counts pass 512, so the launches
+    switch to the kernel variant that reads the weighted-average table from global memory."""
+    o = S.grid_option(24, weighted=True, max_update_num=5000)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True,
+                         max_update_num=5000, weight=0.37)
+    car, orc = make_carver(opt), port.carver(opt)
+    base = S.circle_cameras(7, 64, tilt=0.3)
+    base_masks = [S.silhouette(c, S.SPHERE) for c in base]
+    cams = [base[i % 7] for i in range(700)]
+    masks = [base_masks[i % 7] for i in range(700)]
+    assert car.carve_batch(cams, masks)
+    for c, m in zip(cams, masks):
+        orc.carve_mask(H.to_oracle_camera(c), m)
+    (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+    assert gn.max() > 600 and np.array_equal(gn, wn) and bits_equal(gs, ws)
+
+
+@pytest.mark.parametrize("outside", [0, 1])
+def test_zoomed_cameras_tiles_outside_the_image(cuda_lib, port, outside):
+    """Long focal lengths: most voxel tiles project outside the image (the kernel's "outside"
+    tile class), with UpdateOutsideImage::kNone and ::kMax, both update rules."""
+    for weighted in (False, True):
+        o = S.grid_option(64, weighted=weighted)
+        opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=int(weighted),
+                             truncation=weighted, outside=outside)
+        car, orc = make_carver(opt), port.carver(opt)
+        size = 128
+        for v in range(8):
+            a = 2.0 * np.pi * v / 8
+            pos = (2.5 * np.sin(a), 0.4 * np.cos(2 * a), -2.5 * np.cos(a))
+            c2w = S.look_at_c2w(pos, (0.2 * np.cos(a), 0.1, -0.1))
+            f = (3.0 + v) * size  # field of view far narrower than the grid
+            ocam = B.Camera(size, size, c2w, f, f, size / 2 - 0.5, size / 2 - 0.5)
+            mask = S.silhouette(S.PinholeCamera(size, size, c2w, (size / 2 - 0.5,) * 2, (f, f)),
+                                ((0.2, 0.1, -0.1, 0.08),))
+            ok, got = car.Carve(H.product_camera(ocam), mask, return_sdf=True)
+            assert ok and bits_equal(got, orc.carve_mask(ocam, mask)), v
+        (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+        assert np.array_equal(gn, wn) and bits_equal(gs, ws), weighted

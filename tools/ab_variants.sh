@@ -7,5 +7,5 @@ for lib in build_variants/lib_*.so; do
   out=$(timeout 600 python bench.py --workload $WL --steps 2 --warmup 3 --no-cpu-baseline 2>/dev/null | tail -1)
   echo "$lib | $ok | $(python -c "
 import json,sys
-d=json.loads(sys.argv[1]); print('step %.1f ms fusion %.1f ms sdf %.2f mc %.2f fp32 %.3f'%(d['ms_per_step'], d['stages_ms_per_step']['fusion'], d['stages_ms_per_step']['sdf2d'], d['stages_ms_per_step']['marching_cubes'], d['fp32']['frac']))" "$out")"
+d=json.loads(sys.argv[1]); print('step %.1f ms fusion %.1f ms sdf %.2f mc %.2f'%(d['ms_per_step'], d['stages_ms_per_step']['fusion'], d['stages_ms_per_step']['sdf2d'], d['stages_ms_per_step']['marching_cubes']))" "$out")"
 done
