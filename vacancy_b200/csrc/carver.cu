@@ -340,8 +340,9 @@ int flush_pending(vcb_carver* c) {
     c->fp.tables = static_cast<unsigned char*>(c->fuse_tabs.ptr);
   }
   c->fp.n_views = c->pending;
-  // update_num <= views applied so far, so the `update_num > max` gate cannot fire before that
-  c->fp.cap_possible = c->max_count > (int64_t)c->opt.voxel_max_update_num ? 1 : 0;
+  // the gate tests update_num BEFORE a view is applied: the largest count it can meet in this
+  // launch is (counts so far) + (views of the launch) - 1 = max_count - 1
+  c->fp.cap_possible = c->max_count - 1 > (int64_t)c->opt.voxel_max_update_num ? 1 : 0;
   {
     Span span(c, 1);
     launch_fusion(c->fp, c->opt.sdf_interp, c->opt.voxel_update, c->stream, &c->stage_launches[1]);
