@@ -182,7 +182,7 @@ int vcb_signed_distance_to_color(int32_t device, const float* sdf, int32_t width
  * the library:
  *   - limit: W32 * height <= 2048 * 2048 pixels, W32 = width rounded up to a multiple of 32;
  *     larger images are refused with VCB_ERR_INVALID (use vcb_make_signed_distance_field);
- *   - cost: every GPU that loads the library holds that array (16.5 MiB) until the process exits;
+ *   - cost: every GPU that loads the library holds that array (16.75 MiB) until the process exits;
  *   - the array is shared by all calls and keeps the previous call's contents; each call
  *     re-initialises the cells it accumulates into, but two calls whose kernels overlap on the GPU
  *     (different streams, or different host threads) race on it - serialise them;

@@ -38,8 +38,15 @@ __host__ __device__ inline size_t sdf_plane_bytes(int width, int height) {
 __host__ __device__ inline size_t sdf_bits_bytes(int width, int height) {
   return ((size_t)(sdf_pitch(width) / 32) * height * sizeof(uint32_t) + 255) & ~(size_t)255;
 }
+// value table of the finalize pass (L1 modes): one float per possible signed distance, see
+// sdf_lut_kernel; index = clamp(d, -n, n) + n with n = width + height
+__host__ __device__ inline int sdf_lut_entries(int width, int height) { return 2 * (width + height) + 1; }
+__host__ __device__ inline size_t sdf_lut_bytes(int width, int height) {
+  return ((size_t)sdf_lut_entries(width, height) * sizeof(float) + 255) & ~(size_t)255;
+}
 size_t sdf_scratch_bytes(int width, int height, int mode) {
-  const size_t base = 2 * sdf_plane_bytes(width, height) + sdf_bits_bytes(width, height);
+  const size_t base = 2 * sdf_plane_bytes(width, height) + sdf_bits_bytes(width, height) +
+                      sdf_lut_bytes(width, height);
   // Euclidean mode: parabola stack (two int32 planes) + squared distances (one int32 plane)
   return mode == kSdfSignedL2 ? base + 6 * sdf_plane_bytes(width, height) : base;
 }
@@ -55,10 +62,15 @@ __device__ __forceinline__ int16_t* view_cold(const SdfView& v) {
 __device__ __forceinline__ uint32_t* view_bits(const SdfView& v) {
   return reinterpret_cast<uint32_t*>(v.scratch + 2 * sdf_plane_bytes(v.width, v.height));
 }
+__device__ __forceinline__ float* view_lut(const SdfView& v) {
+  return reinterpret_cast<float*>(v.scratch + 2 * sdf_plane_bytes(v.width, v.height) +
+                                  sdf_bits_bytes(v.width, v.height));
+}
 // int32 planes of the Euclidean mode: 0 = stack of parabolas, 1 = their start rows, 2 = result
 __device__ __forceinline__ int32_t* view_l2_plane(const SdfView& v, int k) {
   return reinterpret_cast<int32_t*>(v.scratch + 2 * sdf_plane_bytes(v.width, v.height) +
                                     sdf_bits_bytes(v.width, v.height) +
+                                    sdf_lut_bytes(v.width, v.height) +
                                     (size_t)k * 2 * sdf_plane_bytes(v.width, v.height));
 }
 
@@ -389,6 +401,106 @@ __global__ void __launch_bounds__(1024) sdf_col_smem_kernel(const __grid_constan
   if (cx == 0 && local_max > 0) atomicMax(v.absmax, local_max);
 }
 
+// ---- pass 2, packed: two columns per thread on the 16-bit SIMD integer instructions ------------
+// (VIADDMNMX.S16x2 / VIMNMX.S16x2 / VIADD.16x2 of sm_100a).  Used when every distance of the batch
+// stays far below 2^15 (launch_sdf2d checks), with kPackInf standing for "no seed yet".
+// Two sweeps over the data instead of three, and no strip in shared memory:
+//   forward  (per segment, no carry): f(y) = min(f(y-1) + 1, g(y)); the signed result fb - fa (one of
+//            the two polarities is 0 on every pixel) goes to the output plane, together with the
+//            segment summaries F = f(last row) and Bl = min_i (f(i) + i);
+//   carries: forward carry cf from the F of the segments above; the true forward value is
+//            min(f(i), cf + i + 1), so the segment's backward summary is B = min(Bl, cf + 1);
+//   backward (with both carries): d(y) = min(d(y+1) + 1, min(f(y), cf + y + 1)), written over f.
+// A column with no pixel of the other class anywhere in the ROI ends with values >= kPackInf; the
+// finalize pass clamps every |d| > width + height to "none", and the maximum is reported as INT_MAX.
+constexpr int kPackSegs = 16;
+constexpr int kPackInf = 0x3FFF;
+constexpr unsigned kPackInf2 = 0x3FFF3FFFu, kPackOne2 = 0x00010001u, kPackMinusOne2 = 0xFFFFFFFFu;
+
+__device__ __forceinline__ unsigned pack_dup(int v) { return (unsigned)(v & 0xFFFF) * 0x00010001u; }
+
+__global__ void __launch_bounds__(32 * kPackSegs, 2)
+    sdf_col_pack_kernel(const __grid_constant__ SdfBatch B) {
+  const SdfView& v = B.v[blockIdx.y];
+  const int lane = threadIdx.x, seg = threadIdx.y;
+  const int xb = (v.rx0 & ~1) + blockIdx.x * 64;
+  if (xb > v.rx1) return;  // whole block outside this view's ROI
+  const int x = xb + 2 * lane;  // columns x, x + 1
+  const bool pair_ok = x <= v.rx1;
+  const unsigned valid = ((x >= v.rx0 && x <= v.rx1) ? 0x0000FFFFu : 0u) |
+                         ((x + 1 >= v.rx0 && x + 1 <= v.rx1) ? 0xFFFF0000u : 0u);
+  const int roi_h = v.ry1 - v.ry0 + 1;
+  const int seglen = (roi_h + kPackSegs - 1) / kPackSegs;
+  const int ys = v.ry0 + seg * seglen;
+  const int rows = max(0, min(seglen, v.ry1 + 1 - ys));
+  const int pitch2 = sdf_pitch(v.width) / 2;  // row pitch in 32-bit words
+  const unsigned* __restrict__ rowd =
+      reinterpret_cast<const unsigned*>(view_rowd(v)) + (size_t)ys * pitch2 + (x >> 1);
+  unsigned* __restrict__ cold =
+      reinterpret_cast<unsigned*>(view_cold(v)) + (size_t)ys * pitch2 + (x >> 1);
+
+  __shared__ unsigned s_fa[kPackSegs][33], s_fb[kPackSegs][33], s_ba[kPackSegs][33],
+      s_bb[kPackSegs][33];
+
+  unsigned fa = kPackInf2, fb = kPackInf2, bla = kPackInf2, blb = kPackInf2;
+  if (pair_ok) {
+    unsigned iv = 0;  // (i, i)
+#pragma unroll 8
+    for (int i = 0; i < rows; i++) {
+      const unsigned r = __ldg(rowd + (size_t)i * pitch2);
+      const unsigned ga = __vmaxs2(__vneg2(r), 0u);  // seeds: 0 on the other class, row distance else
+      const unsigned gb = __vmaxs2(r, 0u);
+      fa = __viaddmin_s16x2(fa, kPackOne2, ga);
+      fb = __viaddmin_s16x2(fb, kPackOne2, gb);
+      bla = __viaddmin_s16x2(fa, iv, bla);
+      blb = __viaddmin_s16x2(fb, iv, blb);
+      iv = __vadd2(iv, kPackOne2);
+      cold[(size_t)i * pitch2] = __vsub2(fb, fa);
+    }
+  }
+  s_fa[seg][lane] = fa;
+  s_fb[seg][lane] = fb;
+  __syncthreads();
+  // forward carry: the recurrence just above this segment, from the segments above (all full)
+  unsigned cfa = kPackInf2, cfb = kPackInf2;
+  for (int s = 0; s < seg; s++) {
+    const unsigned gap = pack_dup((seg - 1 - s) * seglen);
+    cfa = __vmins2(cfa, __vadd2(s_fa[s][lane], gap));
+    cfb = __vmins2(cfb, __vadd2(s_fb[s][lane], gap));
+  }
+  // backward summary of this segment with the carry applied (an empty segment has none)
+  s_ba[seg][lane] = rows > 0 ? __vmins2(bla, __vadd2(cfa, kPackOne2)) : kPackInf2;
+  s_bb[seg][lane] = rows > 0 ? __vmins2(blb, __vadd2(cfb, kPackOne2)) : kPackInf2;
+  __syncthreads();
+  unsigned da = kPackInf2, db = kPackInf2;
+  for (int s = seg + 1; s < kPackSegs; s++) {  // a segment below exists only if this one is full
+    const unsigned gap = pack_dup((s - seg - 1) * seglen);
+    da = __vmins2(da, __vadd2(s_ba[s][lane], gap));
+    db = __vmins2(db, __vadd2(s_bb[s][lane], gap));
+  }
+  unsigned mx = 0;
+  if (pair_ok) {
+    unsigned ca = __vadd2(cfa, pack_dup(rows)), cb = __vadd2(cfb, pack_dup(rows));  // cf + i + 1
+#pragma unroll 8
+    for (int i = rows - 1; i >= 0; i--) {
+      const unsigned f = cold[(size_t)i * pitch2];  // this thread's own forward result
+      const unsigned fat = __vmins2(__vmaxs2(__vneg2(f), 0u), ca);
+      const unsigned fbt = __vmins2(__vmaxs2(f, 0u), cb);
+      da = __viaddmin_s16x2(da, kPackOne2, fat);
+      db = __viaddmin_s16x2(db, kPackOne2, fbt);
+      ca = __vadd2(ca, kPackMinusOne2);
+      cb = __vadd2(cb, kPackMinusOne2);
+      mx = __vmaxs2(mx, __vmaxs2(da, db));
+      cold[(size_t)i * pitch2] = __vsub2(db, da);
+    }
+  }
+  mx &= valid;
+  int local_max = max((int)(mx & 0xFFFFu), (int)(mx >> 16));
+  if (local_max >= kPackInf) local_max = INT_MAX;
+  local_max = __reduce_max_sync(0xffffffffu, local_max);
+  if (lane == 0 && local_max > 0) atomicMax(v.absmax, local_max);
+}
+
 // ---- pass 2 (Euclidean mode): exact squared distance along the column --------------------------
 // No counterpart in the reference (its transform is the L1 one above); offered because hosts may
 // want the true Euclidean silhouette distance.  D2(x, y) = min over y' of (y - y')^2 + g(x, y')^2
@@ -486,24 +598,49 @@ __device__ __forceinline__ float sdf_value(int d, int mode, bool do_norm, float 
   return f;
 }
 
-__global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant__ SdfBatch B,
-                                                           int mode, int normalize, int truncate,
-                                                           float band) {
-  const SdfView& v = B.v[blockIdx.y];
-  const int y0 = blockIdx.x * kTilePx;
-  if (y0 >= v.height) return;
-  float norm = 1.0f;
-  bool do_norm = false;
+// normalisation factor of a view, voxel_carver.cc:205-222 (do_norm false when it does not apply)
+__device__ __forceinline__ float sdf_norm_of(const SdfView& v, int mode, int normalize,
+                                             bool* do_norm) {
+  *do_norm = false;
   if (normalize && (mode == kSdfSigned || mode == kSdfSignedL2)) {
     const int am_i = *v.absmax;
     const float am = am_i == INT_MAX
                          ? FLT_MAX
                          : (mode == kSdfSignedL2 ? (float)__dsqrt_rn((double)am_i) : (float)am_i);
     if (am > FLT_MIN) {  // voxel_carver.cc:213
-      do_norm = true;
-      norm = __fdiv_rn(1.0f, am);
+      *do_norm = true;
+      return __fdiv_rn(1.0f, am);
     }
   }
+  return 1.0f;
+}
+
+// L1 modes: the final value of a pixel depends on its integer distance only, so the conversion,
+// normalisation and truncation run once per possible distance instead of once per pixel.
+// Entry clamp(d, -n, n) + n, n = width + height (no finite distance reaches n); the two ends stand
+// for "no pixel of the other class" (+-kRowInf in the exact passes, >= kPackInf in the packed one).
+__global__ void __launch_bounds__(256) sdf_lut_kernel(const __grid_constant__ SdfBatch B, int mode,
+                                                      int normalize, int truncate, float band) {
+  const SdfView& v = B.v[blockIdx.y];
+  const int n = v.width + v.height;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > 2 * n) return;
+  bool do_norm;
+  const float norm = sdf_norm_of(v, mode, normalize, &do_norm);
+  const int d = i == 0 ? -kRowInf : (i == 2 * n ? (int)kRowInf : i - n);
+  view_lut(v)[i] = sdf_value(d, mode, do_norm, norm, truncate, band);
+}
+
+__global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant__ SdfBatch B,
+                                                           int mode, int normalize, int truncate,
+                                                           float band) {
+  const SdfView& v = B.v[blockIdx.y];
+  const int y0 = blockIdx.x * kTilePx;
+  if (y0 >= v.height) return;
+  bool do_norm = false;
+  const float norm = mode == kSdfSignedL2 ? sdf_norm_of(v, mode, normalize, &do_norm) : 1.0f;
+  const float* __restrict__ lut = view_lut(v);  // L1 modes, see sdf_lut_kernel
+  const int lut_n = v.width + v.height;
   const int pitch = sdf_pitch(v.width);
   const int16_t* __restrict__ cold = view_cold(v);
   const int32_t* __restrict__ d2p = mode == kSdfSignedL2 ? view_l2_plane(v, 2) : nullptr;
@@ -546,9 +683,12 @@ __global__ void __launch_bounds__(256) sdf_finalize_kernel(const __grid_constant
           const int x = x0 + i;
           const int d = dd[i];
           // zeros outside the ROI, voxel_carver.cc:104
-          f[i] = (row_in && x >= v.rx0 && x <= v.rx1)
-                     ? sdf_value(d, mode, do_norm, norm, truncate, band)
-                     : 0.0f;
+          const bool in_roi = row_in && x >= v.rx0 && x <= v.rx1;
+          if (mode == kSdfSignedL2) {
+            f[i] = in_roi ? sdf_value(d, mode, do_norm, norm, truncate, band) : 0.0f;
+          } else {
+            f[i] = in_roi ? __ldg(lut + (min(max(d, -lut_n), lut_n) + lut_n)) : 0.0f;
+          }
           if (x < v.width) {
             tmax = fmaxf(tmax, f[i]);
             ones = ones && (f[i] == 1.0f);
@@ -629,7 +769,7 @@ __global__ void __launch_bounds__(256) sdf_color_kernel(const float* __restrict_
 
 void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normalize, int truncate,
                   float band, cudaStream_t stream, int64_t* launches) {
-  int max_rows = 0, max_cols = 0, max_h = 0, max_words = 0;
+  int max_rows = 0, max_cols = 0, max_h = 0, max_words = 0, max_dist_bound = 0, max_lut = 0;
   SdfBatch views_dev;
   for (int i = 0; i < n_views; i++) {
     const SdfView& v = views_host[i];
@@ -638,6 +778,8 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
     max_cols = max(max_cols, v.rx1 - v.rx0 + 1);
     max_h = max(max_h, v.height);
     max_words = max(max_words, (v.ry1 - v.ry0 + 1) * (sdf_pitch(v.width) / 32));
+    max_dist_bound = max(max_dist_bound, v.width + v.height);
+    max_lut = max(max_lut, sdf_lut_entries(v.width, v.height));
   }
   sdf_bits_kernel<<<dim3((max_words + 255) / 256, n_views), 256, 0, stream>>>(views_dev);
   sdf_row_kernel<<<dim3((max_rows + kRowWarps - 1) / kRowWarps, n_views), kRowWarps * 32, 0,
@@ -645,6 +787,9 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
   const int max_seglen = (max_rows + 31) / 32;
   if (mode == kSdfSignedL2) {
     sdf_col_l2_kernel<<<dim3((max_cols + 127) / 128, n_views), 128, 0, stream>>>(views_dev);
+  } else if (max_dist_bound <= 16000) {
+    sdf_col_pack_kernel<<<dim3((max_cols + 1 + 63) / 64, n_views), dim3(32, kPackSegs), 0, stream>>>(
+        views_dev);
   } else if (max_seglen <= kColMaxSegLen) {
     const size_t smem = (size_t)32 * 32 * max_seglen * sizeof(int16_t);
     static bool attr_set[64] = {false};
@@ -658,6 +803,11 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
     sdf_col_smem_kernel<<<dim3((max_cols + 31) / 32, n_views), dim3(32, 32), smem, stream>>>(views_dev);
   } else {
     sdf_col_kernel<<<dim3((max_cols + 31) / 32, n_views), dim3(32, kColSegs), 0, stream>>>(views_dev);
+  }
+  if (mode != kSdfSignedL2) {
+    sdf_lut_kernel<<<dim3((max_lut + 255) / 256, n_views), 256, 0, stream>>>(views_dev, mode,
+                                                                              normalize, truncate, band);
+    if (launches) *launches += 1;
   }
   sdf_finalize_kernel<<<dim3((max_h + kTilePx - 1) / kTilePx, n_views), 256, 0, stream>>>(
       views_dev, mode, normalize, truncate, band);
@@ -684,9 +834,9 @@ void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_
 // ------------------------------------------------------------------------------------------------
 // vcb_make_signed_distance_field_noalloc: the 2D SDF of one mask without a single allocation.
 //
-// The three kernels above need 4 bytes of scratch per pixel (two int16 images) plus a small
+// The kernels above need 4 bytes of scratch per pixel (two int16 images), a value table and a small
 // descriptor block.  Here that scratch is this fixed array, part of the library image: every GPU
-// that loads libvacancy_b200.so carries it (16.5 MiB) until the process exits, and images of more
+// that loads libvacancy_b200.so carries it (16.75 MiB) until the process exits, and images of more
 // than kNoAllocMaxPixels pixels (width rounded up to a multiple of 32) are refused.  All calls
 // share the one array.
 namespace vcb {
@@ -694,9 +844,11 @@ namespace {
 
 constexpr int64_t kNoAllocMaxPixels = 2048LL * 2048LL;  // counted with the width rounded up to 32
 constexpr size_t kNoAllocHeader = 256;  // abs-max and image-max cells
-// two int16 images + one bit per pixel + their 256-byte alignment slack
-constexpr size_t kNoAllocBytes =
-    kNoAllocHeader + 2 * sizeof(int16_t) * kNoAllocMaxPixels + kNoAllocMaxPixels / 8 + 3 * 256;
+// two int16 images + one bit per pixel + the value table (at most 2 * (16384 + 16384) + 1 floats)
+// + their 256-byte alignment slack
+constexpr size_t kNoAllocBytes = kNoAllocHeader + 2 * sizeof(int16_t) * kNoAllocMaxPixels +
+                                 kNoAllocMaxPixels / 8 + sizeof(float) * (4 * kMaxImageDim + 1) +
+                                 4 * 256;
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
 
