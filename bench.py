@@ -313,7 +313,7 @@ def run_ours(args, cfg):
         if t:  # ncu capture of a full 64-view launch; scale to this run's average views per launch
             traffic = (t["dram_bytes_read"] + t["dram_bytes_write"]) * views_per_launch / \
                 t["views_in_launch"]
-            issue = {k: t[k] for k in ("warp_instructions_per_voxel_view", "issue_active",
+            issue = {k: t[k] for k in ("thread_instructions_per_voxel_view", "issue_active",
                                        "fma_pipe_active", "source") if k in t}
 
     line = {
