@@ -46,6 +46,9 @@ struct TimedSpan {
 
 }  // namespace
 
+constexpr int kMaxStageSets = kMaxViewsPerLaunch / kSdfSubBatch + 2;  // one launch ahead + 2
+constexpr size_t kStageBudgetBytes = (size_t)512 << 20;                // never more than this
+
 struct vcb_carver {
   vcb_options opt;
   int nx = 0, ny = 0, nz = 0;
@@ -79,8 +82,11 @@ struct vcb_carver {
   // host masks are uploaded on a separate stream into a 2-deep ring of staging sets, so that the
   // copy of one sub-batch overlaps the kernels of the previous ones
   cudaStream_t copy_stream = nullptr;
-  cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
-  bool consumed_valid[2] = {false, false};
+  // host masks travel through a ring of staging sets (kSdfSubBatch masks each) on their own copy
+  // stream; with enough sets the copies of the next 64 views run under the current fusion launch
+  cudaEvent_t ev_copied[kMaxStageSets] = {}, ev_consumed[kMaxStageSets] = {};
+  bool consumed_valid[kMaxStageSets] = {};
+  int stage_sets = 2;
   unsigned stage_round = 0;
   size_t sdf_pix = 0;      // mask staging bytes per view
   size_t sdf_scr = 0;      // 2D-SDF scratch bytes per view
@@ -369,10 +375,16 @@ int ensure_sdf_scratch(vcb_carver* c, size_t pix, size_t scr) {
   scr = scr > c->sdf_scr ? scr : c->sdf_scr;
   pix = (pix + 255) & ~(size_t)255;
   if (c->copy_stream) CU(c, cudaStreamSynchronize(c->copy_stream));
-  CU(c, c->mask_stage.reserve(pix * kSdfSubBatch * 2));
+  {
+    size_t sets = kStageBudgetBytes / (pix * kSdfSubBatch);
+    sets = sets < 2 ? 2 : (sets > (size_t)kMaxStageSets ? (size_t)kMaxStageSets : sets);
+    c->stage_sets = (int)sets;
+  }
+  CU(c, c->mask_stage.reserve(pix * kSdfSubBatch * c->stage_sets));
   CU(c, c->sdf_scratch.reserve(scr * kSdfSubBatch));
   CU(c, c->absmax.reserve(sizeof(int) * kSdfSubBatch));
-  c->consumed_valid[0] = c->consumed_valid[1] = false;
+  for (int s2 = 0; s2 < kMaxStageSets; s2++) c->consumed_valid[s2] = false;
+  c->stage_round = 0;
   c->sdf_pix = pix;
   c->sdf_scr = scr;
   return VCB_OK;
@@ -409,7 +421,7 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
   float* max_sdf = static_cast<float*>(c->max_sdf.ptr);
   if (!device_io && c->copy_stream == nullptr) {
     CU(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-    for (int s = 0; s < 2; s++) {
+    for (int s = 0; s < kMaxStageSets; s++) {
       CU(c, cudaEventCreateWithFlags(&c->ev_copied[s], cudaEventDisableTiming));
       CU(c, cudaEventCreateWithFlags(&c->ev_consumed[s], cudaEventDisableTiming));
     }
@@ -418,7 +430,7 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
     int nb = min(kSdfSubBatch, n_views - first);
     nb = min(nb, kMaxViewsPerLaunch - c->pending);
     SdfView hv[kSdfSubBatch];
-    const int set = (int)(c->stage_round & 1u);
+    const int set = (int)(c->stage_round % (unsigned)c->stage_sets);
     if (!device_io && c->consumed_valid[set]) {
       // the staging set may only be overwritten once the kernels that read it have finished
       CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_consumed[set], 0));
@@ -625,7 +637,7 @@ void vcb_destroy(vcb_carver* c) {
   if (c->copy_stream) {
     cudaStreamSynchronize(c->copy_stream);
     cudaStreamDestroy(c->copy_stream);
-    for (int s = 0; s < 2; s++) {
+    for (int s = 0; s < kMaxStageSets; s++) {
       cudaEventDestroy(c->ev_copied[s]);
       cudaEventDestroy(c->ev_consumed[s]);
     }

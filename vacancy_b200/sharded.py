@@ -140,8 +140,16 @@ class _Slab:
         capi.check(self.lib, self.h, self.lib.vcb_extract_iso_faces(self.h))
 
     def mesh_host(self, nv, nf):
-        v = np.empty((nv, 3), np.float32)
-        f = np.empty((nf, 3), np.int32)
+        """This slab's mesh on the host.  The arrays are views of a pinned buffer the slab keeps and
+        reuses (pageable destinations make the copy several times slower): valid until the next
+        call, copy them to keep them."""
+        import torch
+        need = (nv + nf) * 12
+        if getattr(self, "_mesh_pin", None) is None or self._mesh_pin.numel() < need:
+            self._mesh_pin = torch.empty(max(need, 1) * 5 // 4, dtype=torch.uint8, pin_memory=True)
+        raw = self._mesh_pin.numpy()
+        v = raw[:nv * 12].view(np.float32).reshape(nv, 3)
+        f = raw[nv * 12:need].view(np.int32).reshape(nf, 3)
         capi.check(self.lib, self.h, self.lib.vcb_extract_iso_fill(
             self.h, v.ctypes.data_as(C.POINTER(C.c_float)), f.ctypes.data_as(C.POINTER(C.c_int32))))
         return v, f
