@@ -509,3 +509,31 @@ def test_zoomed_cameras_tiles_outside_the_image(cuda_lib, port, outside):
             assert ok and bits_equal(got, orc.carve_mask(ocam, mask)), v
         (gs, gn), (ws, wn) = car.download_grid(), orc.download()
         assert np.array_equal(gn, wn) and bits_equal(gs, ws), weighted
+
+
+def test_huge_image_coordinates(cuda_lib, port):
+    """Cameras inside the grid with absurd focal lengths: image coordinates beyond +-2^22 (where the
+    add-magic floor of the sampling path is not valid), infinities from pc.z == 0 planes and
+    depths next to zero must all end up on the literal path and match the reference bit for bit."""
+    for weighted in (False, True):
+        o = S.grid_option(32, weighted=weighted)
+        opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=int(weighted),
+                             truncation=weighted, outside=int(weighted))
+        car, orc = make_carver(opt), port.carver(opt)
+        size = 64
+        centre = float(np.float32(2.0) / np.float32(32)) * 0.5  # a voxel centre plane: pc.z == 0 there
+        # (pc.z == 0 together with pc.x == 0 would be NaN coordinates - undefined behaviour in the
+        # reference - so no camera sits exactly on a voxel centre in x and y)
+        for v, (pos, f) in enumerate([((0.0, 0.0, 0.0), 1.0e6),
+                                      ((centre + 0.013, centre - 0.021, centre), 3.0e7),
+                                      ((0.3, -0.2, 0.1), 8.0e9), ((0.0, 0.0, -0.5), 2.0e5),
+                                      ((centre, 0.0, -3.0), 70.0)]):
+            c2w = np.eye(4)
+            c2w[:3, 3] = pos
+            ocam = B.Camera(size, size, c2w, f, f * 1.5, size / 2 - 0.5, size / 2 - 0.5)
+            mask = np.zeros((size, size), np.uint8)
+            mask[20:44, 16:40] = 255
+            ok, got = car.Carve(H.product_camera(ocam), mask, return_sdf=True)
+            assert ok and bits_equal(got, orc.carve_mask(ocam, mask)), v
+        (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+        assert np.array_equal(gn, wn) and bits_equal(gs, ws), weighted
