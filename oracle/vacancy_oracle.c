@@ -211,8 +211,8 @@ void vo_make_sdf_l2(const uint8_t* mask, int w, int h, int rx0, int ry0, int rx1
                     int normalize, int truncate, float band, float* dist) {
   size_t n = (size_t)w * (size_t)h, i;
   int x, y;
-  uint8_t* fg = (uint8_t*)malloc(n ? n : 1);
-  uint8_t* bg = (uint8_t*)malloc(n ? n : 1);
+  uint8_t* fg = (uint8_t*)calloc(n ? n : 1, 1);
+  uint8_t* bg = (uint8_t*)calloc(n ? n : 1, 1);
   long long* to_bg = (long long*)malloc((n ? n : 1) * sizeof(long long));
   long long* to_fg = (long long*)malloc((n ? n : 1) * sizeof(long long));
   for (i = 0; i < n; i++) {
