@@ -239,8 +239,9 @@ def run_ours(args, cfg):
     def step_e2e():
         car.reset()
         car.carve_host_masks(cams, host_np)
-        v, f = car.extract_iso_host(0.0, True)
-        return len(v), len(f), v.nbytes + f.nbytes
+        total = car.extract_iso_counts(0.0, True)
+        v, f = car.slab.mesh_host(*car._counts)  # this rank's part of the mesh, global vertex ids
+        return total[0], total[1], v.nbytes + f.nbytes
 
     def timed(fn, steps):
         barrier()
@@ -290,6 +291,8 @@ def run_ours(args, cfg):
     e2e_steps = max(1, min(args.steps, 3))
     ms_e2e_total, e2e_out = timed(step_e2e, e2e_steps)
     ms_e2e = ms_e2e_total / e2e_steps
+    # the host path must produce the mesh of the resident path (same global counts on every rank)
+    assert (int(e2e_out[0]), int(e2e_out[1])) == (int(counts[0]), int(counts[1])), (e2e_out, counts)
 
     nvox = float(n) ** 3
     updates = nvox * V

@@ -259,30 +259,50 @@ class ShardedCarver:
         self.car.carve_device(views, [base + i * stride for i in range(dev_masks.shape[0])],
                               masks=True)
 
-    def carve_host_masks(self, cameras, host_masks):
+    def carve_host_masks(self, cameras, host_masks, chunk=64):
         """Masks in HOST memory (pinned for asynchronous copies). One GPU: straight through the host
         entry point. Several GPUs: every rank uploads only its 1/world share over its own PCIe link
         and the shares are all-gathered over NVLink (NCCL), so no rank moves the whole set from the
-        host; then each rank fuses every view into its slab."""
+        host; then each rank fuses every view into its slab.  The upload + all-gather runs on a side
+        stream in chunks of `chunk` views (one fusion launch), so the masks of the next launch travel
+        while the current one is being fused."""
         if self.world == 1:
             assert self.car.carve_batch(cameras, host_masks)
             return
         torch = self.torch
         n = len(host_masks)
         h, w = host_masks[0].shape
-        per = (n + self.world - 1) // self.world
+        plan, total = [], 0  # (first view, views, views per rank, offset in the device buffer)
+        for first in range(0, n, chunk):
+            cnt = min(chunk, n - first)
+            per = (cnt + self.world - 1) // self.world
+            plan.append((first, cnt, per, total))
+            total += per * self.world
         buf = getattr(self, "_mask_buf", None)
-        if buf is None or tuple(buf.shape) != (self.world * per, h, w):
-            buf = self._mask_buf = torch.empty((self.world * per, h, w), dtype=torch.uint8,
+        if buf is None or tuple(buf.shape) != (total, h, w):
+            buf = self._mask_buf = torch.empty((total, h, w), dtype=torch.uint8,
                                                device=self.slab.device)
-        with torch.cuda.stream(self.stream):
-            lo, hi = self.rank * per, min(n, (self.rank + 1) * per)
-            for i in range(lo, hi):
-                buf[i].copy_(torch.from_numpy(host_masks[i]), non_blocking=True)
-            torch.distributed.all_gather_into_tensor(buf.view(self.world, -1),
-                                                     buf[lo:lo + per].view(-1), group=self.group)
+        side = getattr(self, "_side_stream", None)
+        if side is None:
+            side = self._side_stream = torch.cuda.Stream(device=self.slab.device)
+        side.wait_stream(self.stream)  # kernels of the previous pass may still read the buffer
+        events = []
+        with torch.cuda.stream(side):
+            for first, cnt, per, off in plan:
+                lo, hi = min(cnt, self.rank * per), min(cnt, (self.rank + 1) * per)
+                for i in range(lo, hi):
+                    buf[off + i].copy_(torch.from_numpy(host_masks[first + i]), non_blocking=True)
+                mine = buf[off + self.rank * per:off + (self.rank + 1) * per]
+                torch.distributed.all_gather_into_tensor(
+                    buf[off:off + per * self.world].view(self.world, -1), mine.view(-1),
+                    group=self.group)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                events.append(ev)
         views = self.make_views(cameras, w, h)
-        self.carve_device_masks(views, buf[:n])
+        for (first, cnt, per, off), ev in zip(plan, events):
+            self.stream.wait_event(ev)
+            self.carve_device_masks(views[first:first + cnt], buf[off:off + cnt])
 
     # ---- marching cubes ---------------------------------------------------------------------------
     def _sendrecv(self, send, recv):
