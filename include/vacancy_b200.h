@@ -207,6 +207,24 @@ int vcb_extract_iso_fill(vcb_carver* c, float* vertices, int32_t* faces);
  * until its next extract call or destroy). */
 int vcb_extract_iso_device(vcb_carver* c, const float** vertices_dev, const int32_t** faces_dev);
 
+/* ASCII PLY text of a mesh, byte for byte what Mesh::WritePly (mesh.cc:583-631) writes for a mesh
+ * without vertex colours: the header (:596-612), one line "x y z \n" per vertex (:614-624, floats
+ * as `ofs << float`, i.e. "%g" with 6 significant digits) and one line "3 i j k \n" per face
+ * (:626-629).  The lines are formatted on the GPU with exact integer arithmetic.
+ *   vcb_ply_header     host only; with text == NULL only the size is returned.
+ *   vcb_ply_body_size / _fill   the mesh left on the device by the last vcb_extract_iso_count (or
+ *       the phased calls): sizes of the vertex lines and of the face lines, then both blocks into
+ *       caller buffers of those sizes.  A file is header + vertex block + face block; with z slabs
+ *       it is the header for the global counts, every slab's vertex block in slab order, then every
+ *       slab's face block (ids are already global).
+ *   vcb_ply_format     the whole file from HOST arrays (any mesh); with text == NULL only the size
+ *       is returned. */
+int vcb_ply_header(int64_t n_vertices, int64_t n_faces, char* text, size_t capacity, size_t* n_bytes);
+int vcb_ply_body_size(vcb_carver* c, size_t* vertex_bytes, size_t* face_bytes);
+int vcb_ply_body_fill(vcb_carver* c, char* vertex_text, char* face_text);
+int vcb_ply_format(int32_t device, const float* vertices, int64_t n_vertices, const int32_t* faces,
+                   int64_t n_faces, char* text, size_t capacity, size_t* n_bytes);
+
 /* The same extraction in phases, for a grid sharded into z slabs across GPUs (no reference
  * counterpart: the reference is single-process; numbering still follows marching_cubes.cc:199-218
  * over the WHOLE grid).  Per slab, in this order:

@@ -115,6 +115,7 @@ class RefLib:
                                                C.POINTER(C.c_longlong), c_double_p]
         L.ref_carver_mesh_copy.argtypes = [C.c_void_p, c_float_p, c_int_p]
         L.ref_carver_mesh_write_ply.argtypes = [C.c_void_p, C.c_char_p]
+        L.ref_write_ply.argtypes = [C.c_char_p, c_float_p, C.c_longlong, c_int_p, C.c_longlong]
         L.ref_distance_transform_l1.argtypes = [c_u8_p] + [C.c_int] * 6 + [c_float_p]
         L.ref_make_sdf.argtypes = [c_u8_p] + [C.c_int] * 8 + [C.c_float, c_float_p]
         L.ref_time_make_sdf.restype = C.c_double
@@ -194,6 +195,12 @@ class RefLib:
         out = np.empty((h.value, w.value), np.uint8)
         self.L.ref_load_png_gray(path.encode(), _p(out, c_u8_p), C.byref(w), C.byref(h))
         return out
+
+    def write_ply(self, path, vertices, faces):
+        """Mesh::WritePly of the UNMODIFIED reference on an arbitrary mesh."""
+        v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+        f = np.ascontiguousarray(faces, np.int32).reshape(-1, 3)
+        return self.L.ref_write_ply(path.encode(), _p(v, c_float_p), len(v), _p(f, c_int_p), len(f))
 
     def mc_tables(self):
         e = np.empty(256, np.int32)
@@ -375,6 +382,18 @@ class PortLib:
         out = np.empty(12, np.float32)
         self.L.vo_w2c_from_c2w(_p(c2w, c_double_p), _p(out, c_float_p))
         return out
+
+    def ply_text(self, vertices, faces):
+        """Mesh::WritePly restated (vo_ply_text): the bytes of the ASCII PLY file."""
+        v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+        f = np.ascontiguousarray(faces, np.int32).reshape(-1, 3)
+        self.L.vo_ply_text.restype = C.c_int64
+        self.L.vo_ply_text.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p,
+                                       C.c_int64]
+        n = self.L.vo_ply_text(v.ctypes.data, len(v), f.ctypes.data, len(f), None, 0)
+        out = np.empty(n, np.uint8)
+        self.L.vo_ply_text(v.ctypes.data, len(v), f.ctypes.data, len(f), out.ctypes.data, n)
+        return out.tobytes()
 
     def mc_tables(self):
         e = np.empty(256, np.int32)

@@ -361,6 +361,21 @@ int ref_carver_mesh_write_ply(void* h, const char* path) {
   return rc->mesh.WritePly(path) ? 0 : 1;
 }
 
+// mesh.cc:583-631 ASCII PLY of an arbitrary mesh given as arrays; returns 0 on success
+int ref_write_ply(const char* path, const float* vertices, long long n_vertices, const int* faces,
+                  long long n_faces) {
+  std::vector<Eigen::Vector3f> v(static_cast<size_t>(n_vertices));
+  std::vector<Eigen::Vector3i> f(static_cast<size_t>(n_faces));
+  for (long long i = 0; i < n_vertices; i++)
+    v[i] = Eigen::Vector3f(vertices[3 * i], vertices[3 * i + 1], vertices[3 * i + 2]);
+  for (long long i = 0; i < n_faces; i++)
+    f[i] = Eigen::Vector3i(faces[3 * i], faces[3 * i + 1], faces[3 * i + 2]);
+  vacancy::Mesh mesh;
+  mesh.set_vertices(v);
+  mesh.set_vertex_indices(f);
+  return mesh.WritePly(path) ? 0 : 1;
+}
+
 // Bourke tables as the reference ships them (marching_cubes_lut.cc:15-298)
 void ref_mc_tables(int* edge_table256, int* tri_table256x16);
 

@@ -5,6 +5,7 @@
 
 #include <float.h>
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -686,3 +687,32 @@ void vo_marching_cubes(const int* dims, const float* px, const float* py, const 
 }
 
 void vo_free(void* p) { free(p); }
+
+/* ---- Mesh::WritePly, mesh.cc:583-631 (no vertex colours) ------------------------------------- */
+int64_t vo_ply_text(const float* vertices, int64_t n_vertices, const int32_t* faces, int64_t n_faces,
+                    char* text, int64_t capacity) {
+  char line[320];
+  int64_t n = 0, i;
+  int k;
+  /* header, mesh.cc:596-612 */
+  k = snprintf(line, sizeof(line),
+               "ply\nformat ascii 1.0\nelement vertex %lld\nproperty float x\nproperty float y\n"
+               "property float z\nelement face %lld\nproperty list uchar int vertex_indices\n"
+               "end_header\n",
+               (long long)n_vertices, (long long)n_faces);
+  if (text && n + k <= capacity) memcpy(text + n, line, (size_t)k);
+  n += k;
+  for (i = 0; i < n_vertices; i++) { /* mesh.cc:614-624 */
+    k = snprintf(line, sizeof(line), "%g %g %g \n", (double)vertices[3 * i],
+                 (double)vertices[3 * i + 1], (double)vertices[3 * i + 2]);
+    if (text && n + k <= capacity) memcpy(text + n, line, (size_t)k);
+    n += k;
+  }
+  for (i = 0; i < n_faces; i++) { /* mesh.cc:626-629 */
+    k = snprintf(line, sizeof(line), "3 %d %d %d \n", faces[3 * i], faces[3 * i + 1],
+                 faces[3 * i + 2]);
+    if (text && n + k <= capacity) memcpy(text + n, line, (size_t)k);
+    n += k;
+  }
+  return n;
+}

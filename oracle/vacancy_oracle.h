@@ -98,6 +98,12 @@ void vo_marching_cubes(const int* dims3, const float* px, const float* py, const
                        int32_t** faces, int64_t* n_faces);
 void vo_free(void* p);
 
+/* Mesh::WritePly, mesh.cc:583-631, for a mesh without vertex colours: writes the file's bytes into
+ * text (capacity bytes) and returns their number (the needed size when text is NULL or too small).
+ * `ofs << float` is printf("%g"), `<< int` printf("%d"), std::endl a newline. */
+int64_t vo_ply_text(const float* vertices, int64_t n_vertices, const int32_t* faces, int64_t n_faces,
+                    char* text, int64_t capacity);
+
 /* tables: packed triangle table and the derived edge table (marching_cubes_lut.cc:15-298) */
 void vo_mc_tables(int* edge_table256, int* tri_table256x16);
 

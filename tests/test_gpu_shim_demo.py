@@ -65,7 +65,14 @@ def test_pointer_batch_overload(tmp_path):
     demo = os.path.join(REF_DIR, "batch_demo_b200")
     if not os.path.exists(demo):
         pytest.skip("prebuilt batch demo not present under oracle/_ref")
-    r = subprocess.run([demo, os.path.join(REF_DIR, "data") + "/"], capture_output=True, text=True,
-                       timeout=300)
+    r = subprocess.run([demo, os.path.join(REF_DIR, "data") + "/", str(tmp_path)],
+                       capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.split() == ["8672", "17270", "28475"]
+    # the PLY written by the reference's own Mesh::WritePly and by the two GPU-side writers
+    with open(tmp_path / "surface_reference_writer.ply", "rb") as f:
+        want = f.read()
+    assert want.startswith(b"ply\nformat ascii 1.0\nelement vertex 8672\n")
+    for name in ("surface_gpu_writer.ply", "surface_gpu_direct.ply"):
+        with open(tmp_path / name, "rb") as f:
+            assert f.read() == want, name

@@ -49,6 +49,7 @@ EXPORTS = [
     "vcb_extract_iso_import_bottom", "vcb_extract_iso_faces", "vcb_halo_device",
     "vcb_extract_voxel_count", "vcb_extract_voxel_fill", "vcb_extract_voxel_occupancy",
     "vcb_download_grid", "vcb_upload_grid", "vcb_grid_device", "vcb_stage_times",
+    "vcb_ply_header", "vcb_ply_body_size", "vcb_ply_body_fill", "vcb_ply_format",
 ]
 
 _lib = None
@@ -113,6 +114,11 @@ def load_library(path=LIB_PATH):
     L.vcb_upload_grid.argtypes = [vp, fp, ip]
     L.vcb_grid_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     L.vcb_stage_times.argtypes = [vp, fp, C.POINTER(i64)]
+    szp = C.POINTER(C.c_size_t)
+    L.vcb_ply_header.argtypes = [i64, i64, C.c_char_p, C.c_size_t, szp]
+    L.vcb_ply_body_size.argtypes = [vp, szp, szp]
+    L.vcb_ply_body_fill.argtypes = [vp, vp, vp]
+    L.vcb_ply_format.argtypes = [i32, fp, i64, ip, i64, vp, C.c_size_t, szp]
     _lib = L
     return L
 

@@ -309,6 +309,29 @@ class VoxelCarver:
             self._h, v.ctypes.data_as(C.POINTER(C.c_float)), f.ctypes.data_as(C.POINTER(C.c_int32))))
         return v, f
 
+    def ExtractIsoSurfacePly(self, iso_level=0.0, linear_interp=True):
+        """ExtractIsoSurface + Mesh::WritePly (mesh.cc:583-631) in one go: the bytes of the ASCII PLY
+        file the reference would write for this mesh, formatted on the GPU (examples.cc:143-144)."""
+        nv, nf = self.ExtractIsoSurface(iso_level, linear_interp, copy=False)
+        return self.ply_text(nv, nf)
+
+    def ply_text(self, n_vertices=None, n_faces=None, header=True):
+        """PLY text of the mesh left on the device by the last extraction; with z slabs pass the
+        GLOBAL counts for the header (or header=False) - see vcb_ply_body_size."""
+        vb, fb = C.c_size_t(), C.c_size_t()
+        self._check(self._lib.vcb_ply_body_size(self._h, C.byref(vb), C.byref(fb)))
+        hb = C.c_size_t(0)
+        if header:
+            self._lib.vcb_ply_header(int(n_vertices), int(n_faces), None, 0, C.byref(hb))
+        out = np.empty(hb.value + vb.value + fb.value, np.uint8)
+        if header:
+            self._lib.vcb_ply_header(int(n_vertices), int(n_faces),
+                                     out.ctypes.data_as(C.c_char_p), out.size, None)
+        base = out.ctypes.data
+        self._check(self._lib.vcb_ply_body_fill(self._h, C.c_void_p(base + hb.value),
+                                                C.c_void_p(base + hb.value + vb.value)))
+        return out.tobytes()
+
     def ExtractVoxel(self, inside_empty=False, copy=True):
         n = C.c_int64()
         self._check(self._lib.vcb_extract_voxel_count(self._h, int(inside_empty), C.byref(n)))
@@ -409,6 +432,25 @@ def make_signed_distance_field(mask, roi_min=None, roi_max=None, minmax_normaliz
         int(minmax_normalize), int(use_truncation), C.c_float(truncation_band),
         out.ctypes.data_as(C.POINTER(C.c_float))))
     return out
+
+
+def ply_format(vertices, faces, device=0):
+    """Mesh::WritePly (mesh.cc:583-631) for any mesh without vertex colours: the bytes of the ASCII
+    PLY file, formatted on the GPU."""
+    L = capi.load_library()
+    v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+    f = np.ascontiguousarray(faces, np.int32).reshape(-1, 3)
+    n = C.c_size_t()
+    vp_, fp_ = v.ctypes.data_as(C.POINTER(C.c_float)), f.ctypes.data_as(C.POINTER(C.c_int32))
+    rc = L.vcb_ply_format(device, vp_, len(v), fp_, len(f), None, 0, C.byref(n))
+    if rc != 0:
+        raise capi.VcbError(rc, L.vcb_last_error(None).decode())
+    out = np.empty(n.value, np.uint8)
+    rc = L.vcb_ply_format(device, vp_, len(v), fp_, len(f), C.c_void_p(out.ctypes.data), out.size,
+                          C.byref(n))
+    if rc != 0:
+        raise capi.VcbError(rc, L.vcb_last_error(None).decode())
+    return out.tobytes()
 
 
 def signed_distance_to_color(sdf, min_negative_d, max_positive_d, device=0):

@@ -74,6 +74,7 @@ struct vcb_carver {
   size_t slot_floats = 0;
   Scratch max_sdf;       // one float per slot
   Scratch fuse_tabs;     // per-launch tables of the fusion kernel (fusion_table_bytes)
+  PlyText ply;           // ASCII PLY text of the last extracted mesh (vcb_ply_body_*)
   Scratch tiles;         // 8x8-block flags per slot (tile_flag_bytes), see fusion.cu
   size_t tile_slot_bytes = 0;
   bool use_tiles = true;
@@ -648,7 +649,7 @@ void vcb_destroy(vcb_carver* c) {
   cudaFree(c->pos_y);
   cudaFree(c->pos_z);
   cudaFree(c->wtab);
-  Scratch* all[] = {&c->pool, &c->max_sdf, &c->tiles, &c->fuse_tabs, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
+  Scratch* all[] = {&c->pool, &c->max_sdf, &c->tiles, &c->fuse_tabs, &c->ply.lens, &c->ply.tmp, &c->ply.text, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
                     &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo};
@@ -1012,6 +1013,46 @@ int vcb_extract_iso_device(vcb_carver* c, const float** vertices_dev, const int3
   if (c->iso.phase != 3) return fail(c, VCB_ERR_STATE, "vcb_extract_iso_count has not run");
   if (vertices_dev) *vertices_dev = static_cast<const float*>(c->iso.verts.ptr);
   if (faces_dev) *faces_dev = static_cast<const int32_t*>(c->iso.faces.ptr);
+  return VCB_OK;
+}
+
+int vcb_ply_body_size(vcb_carver* c, size_t* vertex_bytes, size_t* face_bytes) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (c->iso.phase != 3) return fail(c, VCB_ERR_STATE, "no extracted mesh: run vcb_extract_iso_count first");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  {
+    Span span(c, 3);
+    CU(c, ply_measure(static_cast<const float*>(c->iso.verts.ptr), c->iso.n_vertices,
+                      static_cast<const int32_t*>(c->iso.faces.ptr), c->iso.n_faces, &c->ply,
+                      c->stream, &c->stage_launches[3]));
+  }
+  if (vertex_bytes) *vertex_bytes = (size_t)c->ply.vertex_bytes;
+  if (face_bytes) *face_bytes = (size_t)c->ply.face_bytes;
+  return VCB_OK;
+}
+
+int vcb_ply_body_fill(vcb_carver* c, char* vertex_text, char* face_text) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  if (c->iso.phase != 3 || !c->ply.sized || c->ply.nv != c->iso.n_vertices ||
+      c->ply.nf != c->iso.n_faces)
+    return fail(c, VCB_ERR_STATE, "vcb_ply_body_size has not run for this mesh");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  {
+    Span span(c, 3);
+    CU(c, ply_emit(static_cast<const float*>(c->iso.verts.ptr),
+                   static_cast<const int32_t*>(c->iso.faces.ptr), &c->ply, c->stream,
+                   &c->stage_launches[3]));
+  }
+  const char* text = static_cast<const char*>(c->ply.text.ptr);
+  if (vertex_text && c->ply.vertex_bytes > 0)
+    CU(c, cudaMemcpyAsync(vertex_text, text, (size_t)c->ply.vertex_bytes, cudaMemcpyDeviceToHost,
+                          c->stream));
+  if (face_text && c->ply.face_bytes > 0)
+    CU(c, cudaMemcpyAsync(face_text, text + c->ply.vertex_bytes, (size_t)c->ply.face_bytes,
+                          cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
   return VCB_OK;
 }
 

@@ -148,6 +148,18 @@ cudaError_t voxel_extract_fill(const GridDesc& g, VoxelExtract* st, float* verti
 cudaError_t voxel_extract_flags(const GridDesc& g, VoxelExtract* st, uint8_t* flags_host,
                                 cudaStream_t stream, int64_t* launches);
 
+// ---- ASCII PLY text of a device-resident mesh (ply.cu) ----
+struct PlyText {
+  Scratch lens, tmp, text;  // per-line offsets, scan scratch, the characters (vertex lines, then faces)
+  uint64_t vertex_bytes = 0, face_bytes = 0;
+  int64_t nv = 0, nf = 0;
+  bool sized = false;
+};
+cudaError_t ply_measure(const float* verts_dev, int64_t nv, const int32_t* faces_dev, int64_t nf,
+                        PlyText* st, cudaStream_t stream, int64_t* launches);
+cudaError_t ply_emit(const float* verts_dev, const int32_t* faces_dev, PlyText* st,
+                     cudaStream_t stream, int64_t* launches);
+
 struct IsoExtract {
   Scratch ibits, vbits, cbits, abits, segcnt, segbase, active, tmp, hkeys, hvals, verts, faces,
       counters, cinfo;

@@ -1,6 +1,9 @@
 // Small host program against the reference's headers + vacancy_b200_batch.h: the bunny scenario of
 // examples.cc (same bounding box, intrinsics and poses) carved with ONE CarveBatch call, then
-// the iso surface; prints "vertices faces occupied_cubes" for tests/test_gpu_shim_demo.py.
+// the iso surface; prints "vertices faces occupied_cubes" for tests/test_gpu_shim_demo.py.  With a
+// second argument (an output directory) it also writes the iso surface three ways - the reference's
+// Mesh::WritePly, vacancy_b200::WritePly and vacancy_b200::ExtractIsoSurfaceToPly - so that the test
+// can compare the files byte for byte.
 #include <cstdio>
 #include <fstream>
 #include <memory>
@@ -52,5 +55,11 @@ int main(int argc, char* argv[]) {
   carver.ExtractVoxel(&voxels);
   std::printf("%zu %zu %zu\n", mesh.vertices().size(), mesh.vertex_indices().size(),
               voxels.vertices().size() / 24);
+  if (argc > 2) {
+    const std::string out = argv[2];
+    if (!mesh.WritePly(out + "/surface_reference_writer.ply")) return 4;
+    if (!vacancy_b200::WritePly(mesh, out + "/surface_gpu_writer.ply")) return 5;
+    if (!vacancy_b200::ExtractIsoSurfaceToPly(&carver, out + "/surface_gpu_direct.ply", 0.0)) return 6;
+  }
   return 0;
 }

@@ -15,6 +15,7 @@
 // `voxel_grid_` member is simply never allocated (the grid lives on the device as SoA).
 #include "vacancy/voxel_carver.h"
 
+#include <cstdio>
 #include <cstring>
 #include <limits>
 #include <mutex>
@@ -356,6 +357,64 @@ bool CarveBatch(vacancy::VoxelCarver* carver, const std::vector<const vacancy::C
   return report(h, vcb_carve_masks(h, static_cast<int32_t>(views.size()), views.data(),
                                    masks.data(), nullptr),
                 "CarveBatch");
+}
+
+namespace {
+bool write_file(const std::string& path, const std::vector<char>& text) {
+  FILE* f = fopen(path.c_str(), "wb");
+  if (f == nullptr) {
+    vacancy::LOGE("couldn't open ply: %s\n", path.c_str());  // mesh.cc:586-589
+    return false;
+  }
+  const bool ok = text.empty() || fwrite(text.data(), 1, text.size(), f) == text.size();
+  return fclose(f) == 0 && ok;
+}
+}  // namespace
+
+bool ExtractIsoSurfaceToPly(vacancy::VoxelCarver* carver, const std::string& ply_path,
+                            double iso_level, bool linear_interp) {
+  vcb_carver* h = carver ? find_carver(carver) : nullptr;
+  if (h == nullptr) {
+    vacancy::LOGE("ExtractIsoSurfaceToPly: voxel grid has not been initialized\n");
+    return false;
+  }
+  int64_t nv = 0, nf = 0;
+  if (!report(h, vcb_extract_iso_count(h, iso_level, linear_interp ? 1 : 0, &nv, &nf),
+              "ExtractIsoSurfaceToPly"))
+    return false;
+  size_t hb = 0, vb = 0, fb = 0;
+  vcb_ply_header(nv, nf, nullptr, 0, &hb);
+  if (!report(h, vcb_ply_body_size(h, &vb, &fb), "ExtractIsoSurfaceToPly")) return false;
+  std::vector<char> text(hb + vb + fb);
+  vcb_ply_header(nv, nf, text.data(), text.size(), nullptr);
+  if (!report(h, vcb_ply_body_fill(h, text.data() + hb, text.data() + hb + vb),
+              "ExtractIsoSurfaceToPly"))
+    return false;
+  return write_file(ply_path, text);
+}
+
+bool WritePly(const vacancy::Mesh& mesh, const std::string& ply_path, int device) {
+  if (!mesh.vertex_colors().empty()) {  // colours are not covered: the reference's own writer
+    return mesh.WritePly(ply_path);
+  }
+  const auto& v = mesh.vertices();
+  const auto& f = mesh.vertex_indices();
+  static_assert(sizeof(Eigen::Vector3f) == 12 && sizeof(Eigen::Vector3i) == 12, "packed triples");
+  const float* vp = v.empty() ? nullptr : v[0].data();
+  const int32_t* fp = f.empty() ? nullptr : f[0].data();
+  size_t n = 0;
+  if (vcb_ply_format(device, vp, static_cast<int64_t>(v.size()), fp, static_cast<int64_t>(f.size()),
+                     nullptr, 0, &n) != VCB_OK) {
+    vacancy::LOGE("WritePly: %s\n", vcb_last_error(nullptr));
+    return false;
+  }
+  std::vector<char> text(n);
+  if (vcb_ply_format(device, vp, static_cast<int64_t>(v.size()), fp, static_cast<int64_t>(f.size()),
+                     text.data(), text.size(), &n) != VCB_OK) {
+    vacancy::LOGE("WritePly: %s\n", vcb_last_error(nullptr));
+    return false;
+  }
+  return write_file(ply_path, text);
 }
 
 }  // namespace vacancy_b200
