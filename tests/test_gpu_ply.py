@@ -70,3 +70,15 @@ def test_bunny_iso_surface_ply(cuda_lib, port, bunny):
             assert rc.write_ply(path) == 0
             with open(path, "rb") as fh:
                 assert text == fh.read()
+
+
+def test_slab_text_blocks_assemble_to_the_unsharded_file(cuda_lib, port, bunny):
+    """z slabs: header for the global counts + every slab's vertex block + every slab's face block
+    is the file of the unsharded mesh."""
+    from vacancy_b200 import sharded
+    opt = H.product_options(H.oracle_options(bunny.bb_min, bunny.bb_max, H.BUNNY_RESOLUTION))
+    cams = [H.product_camera(H.bunny_camera(bunny, i), bunny.w2c[i]) for i in range(6)]
+    slabs = sharded.LocalSlabs(opt, 3)
+    slabs.carve_batch(cams, [bunny.masks[i] for i in range(6)])
+    v, f = slabs.extract_iso(0.0, True)
+    assert slabs.ply_text() == port.ply_text(v, f)

@@ -315,9 +315,10 @@ class VoxelCarver:
         nv, nf = self.ExtractIsoSurface(iso_level, linear_interp, copy=False)
         return self.ply_text(nv, nf)
 
-    def ply_text(self, n_vertices=None, n_faces=None, header=True):
+    def ply_text(self, n_vertices=None, n_faces=None, header=True, split=False):
         """PLY text of the mesh left on the device by the last extraction; with z slabs pass the
-        GLOBAL counts for the header (or header=False) - see vcb_ply_body_size."""
+        GLOBAL counts for the header (or header=False) - see vcb_ply_body_size.  split=True returns
+        (vertex_text, face_text) instead of one string (slabs: the blocks interleave)."""
         vb, fb = C.c_size_t(), C.c_size_t()
         self._check(self._lib.vcb_ply_body_size(self._h, C.byref(vb), C.byref(fb)))
         hb = C.c_size_t(0)
@@ -330,6 +331,8 @@ class VoxelCarver:
         base = out.ctypes.data
         self._check(self._lib.vcb_ply_body_fill(self._h, C.c_void_p(base + hb.value),
                                                 C.c_void_p(base + hb.value + vb.value)))
+        if split:
+            return out[:hb.value + vb.value].tobytes(), out[hb.value + vb.value:].tobytes()
         return out.tobytes()
 
     def ExtractVoxel(self, inside_empty=False, copy=True):

@@ -77,6 +77,17 @@ def gather_offsets(nv, nf, world, group=None, device="cpu"):
     return exclusive_offsets(torch.stack(allc).cpu().numpy())
 
 
+def assemble_ply(totals, parts):
+    """totals = global (vertices, faces); parts = per-slab (vertex_text, face_text) in slab order."""
+    from . import capi as _capi
+    lib = _capi.load_library()
+    n = C.c_size_t()
+    lib.vcb_ply_header(int(totals[0]), int(totals[1]), None, 0, C.byref(n))
+    head = C.create_string_buffer(n.value)
+    lib.vcb_ply_header(int(totals[0]), int(totals[1]), head, n.value, None)
+    return head.raw + b"".join(p[0] for p in parts) + b"".join(p[1] for p in parts)
+
+
 class _DevArray:
     """Exposes raw device memory of the carver to torch through __cuda_array_interface__."""
 
@@ -195,7 +206,14 @@ class LocalSlabs:
         for s in self.slabs:
             s.faces()
         parts = [s.mesh_host(*c) for s, c in zip(self.slabs, counts)]
+        self._totals = (int(total[0]), int(total[1]))
         return np.concatenate([p[0] for p in parts]), np.concatenate([p[1] for p in parts])
+
+    def ply_text(self):
+        """ASCII PLY of the mesh of the last extract_iso, assembled from the slabs' text blocks:
+        header for the global counts, every slab's vertex lines, then every slab's face lines."""
+        return assemble_ply(self._totals, [s.car.ply_text(header=False, split=True)
+                                           for s in self.slabs])
 
     def occupancy(self, inside_empty=False):
         parts = [s.car.occupancy(inside_empty) for s in self.slabs]
@@ -348,6 +366,20 @@ class ShardedCarver:
         """Extraction + copy of THIS rank's part of the mesh to the host (vertex ids are global)."""
         self.extract_iso_counts(iso, interp)
         return self.slab.mesh_host(*self._counts)
+
+    def ply_parts(self):
+        """(vertex_text, face_text) of THIS rank's part of the last extracted mesh (global ids)."""
+        return self.car.ply_text(header=False, split=True)
+
+    def ply_text_on_rank0(self, totals):
+        """Gathers every rank's text blocks on rank 0 and returns the whole file there (None on
+        the other ranks); totals = the global counts extract_iso_counts returned."""
+        mine = self.ply_parts()
+        if self.world == 1:
+            return assemble_ply(totals, [mine])
+        parts = [None] * self.world if self.rank == 0 else None
+        self.torch.distributed.gather_object(mine, parts, dst=0, group=self.group)
+        return assemble_ply(totals, parts) if self.rank == 0 else None
 
     def stage_times(self):
         return self.car.stage_times()
