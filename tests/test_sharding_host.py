@@ -36,6 +36,20 @@ def test_rebalanced_ranges():
     # degenerate costs still leave every slab its two halo planes
     tiny = sharded.rebalanced_ranges(sharded.slab_ranges(8, 4), [100.0, 0.0, 0.0, 0.0])
     assert all(b - a >= 2 for a, b in tiny) and tiny[-1][1] == 8
+    # whole fusion tiles: every boundary a multiple of the quantum, still contiguous and complete
+    q = sharded.FUSION_TILE_PLANES
+    for costs in ([118.8, 105.8, 102.5, 102.5, 101.9, 102.9, 106.5, 118.5], [1.0] * 8,
+                  [53.5, 51.0, 52.0, 51.0, 50.5, 51.4, 50.1, 49.4]):
+        new = sharded.rebalanced_ranges(ranges, costs, quantum=q)
+        assert new[0][0] == 0 and new[-1][1] == 1024
+        assert all(a[1] == b[0] and a[1] % q == 0 for a, b in zip(new[:-1], new[1:]))
+        assert all(b - a >= q for a, b in new)
+    assert sharded.rebalanced_ranges(ranges, [1.0] * 8, quantum=q) == ranges
+    # too few planes for whole tiles: falls back to single planes
+    tiny = sharded.rebalanced_ranges(sharded.slab_ranges(8, 4), [100.0, 0.0, 0.0, 0.0], quantum=q)
+    assert all(b - a >= 2 for a, b in tiny) and tiny[-1][1] == 8
+    odd = sharded.rebalanced_ranges(sharded.slab_ranges(54, 3), [3.0, 2.0, 1.0], quantum=q)
+    assert odd[0][0] == 0 and odd[-1][1] == 54 and all(b - a >= 2 for a, b in odd)
 
 
 def test_exclusive_offsets():

@@ -38,22 +38,35 @@ def slab_ranges(nz, world):
     return out
 
 
-def rebalanced_ranges(ranges, cost, min_planes=2):
+FUSION_TILE_PLANES = 8  # z planes per fusion tile (kZT in csrc/fusion.cu): a slab pays for whole tiles
+
+
+def rebalanced_ranges(ranges, cost, min_planes=2, quantum=1):
     """New contiguous z ranges with (approximately) equal cost, given the measured cost of each
     current slab (e.g. its fusion time); the cost per plane is taken as constant inside a slab.
+    With quantum > 1 the boundaries are multiples of `quantum` planes and a slab's cost is spread
+    over the whole tiles it pays for (the fusion kernel works on tiles of FUSION_TILE_PLANES planes
+    counted from the slab's first plane, so planes short of a whole tile are wasted work).
     Deterministic, so every rank computes the same partition from the gathered costs."""
     world = len(ranges)
     nz = ranges[-1][1]
+    q = max(1, int(quantum))
+    if nz < world * max(min_planes, q):
+        q = 1  # too few planes to hand out whole tiles
     density = np.empty(nz, np.float64)
     for (a, b), c in zip(ranges, cost):
-        density[a:b] = max(float(c), 1e-9) / (b - a)
+        paid = -(-(b - a) // q) * q
+        density[a:b] = max(float(c), 1e-9) / paid
     cum = np.concatenate([[0.0], np.cumsum(density)])
+    step = max(min_planes, q)
     bounds = [0]
     for r in range(1, world):
         target = cum[-1] * r / world
         z = int(np.searchsorted(cum, target))
-        z = max(z, bounds[-1] + min_planes)
-        z = min(z, nz - min_planes * (world - r))
+        if q > 1:
+            z = int(round(z / q)) * q
+        z = max(z, bounds[-1] + step)
+        z = min(z, (nz - step * (world - r)) // q * q if q > 1 else nz - step * (world - r))
         bounds.append(z)
     bounds.append(nz)
     return [(bounds[i], bounds[i + 1]) for i in range(world)]
@@ -254,7 +267,7 @@ class ShardedCarver:
         allc = [torch.empty_like(mine) for _ in range(self.world)]
         torch.distributed.all_gather(allc, mine, group=self.group)
         cost = [float(t.item()) for t in allc]
-        new = rebalanced_ranges(self.ranges, cost)
+        new = rebalanced_ranges(self.ranges, cost, quantum=FUSION_TILE_PLANES)
         if new != self.ranges:
             self.ranges = new
             self.car.synchronize()
