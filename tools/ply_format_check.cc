@@ -33,7 +33,9 @@ static int check_float(uint32_t bits, long long* bad) {
 }
 
 int main(int argc, char** argv) {
-  const long long per_exp = argc > 1 ? atoll(argv[1]) : 100000;
+  // "all": every one of the 2^32 bit patterns (a few minutes on 8 cores)
+  const bool all = argc > 1 && strcmp(argv[1], "all") == 0;
+  const long long per_exp = all ? 0 : (argc > 1 ? atoll(argv[1]) : 100000);
   long long checked = 0, bad = 0;
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : checked, bad)
   for (int expo = 0; expo < 256; expo++) {
@@ -44,6 +46,11 @@ int main(int argc, char** argv) {
       for (long long i = 0; i < per_exp; i++) {  // random mantissas
         lb += check_float(base | (uint32_t)(rng_next(&s) & 0x7fffffu), &bad);
         checked++;
+      }
+      if (all) {
+        for (uint32_t mnt = 0; mnt < (1u << 23); mnt++) lb += check_float(base | mnt, &bad);
+        checked += 1ll << 23;
+        continue;
       }
       for (uint32_t mnt = 0; mnt < 4096; mnt++) {  // sparse mantissas: few set bits, both ends
         lb += check_float(base | mnt, &bad);
