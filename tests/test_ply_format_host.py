@@ -57,3 +57,20 @@ def test_ply_header_entry_point(port):
     want = port.ply_text(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32))
     assert buf.raw == want.replace(b"vertex 0", b"vertex 1234567").replace(b"face 0", b"face 89")
     assert L.vcb_ply_header(1, 1, buf, 10, None) != 0  # buffer too small
+
+
+def test_slab_blocks_assemble_under_one_header(port):
+    """sharded.assemble_ply: header for the global counts, every slab's vertex lines, then every
+    slab's face lines - checked with the oracle's text cut into two fake slabs (host only)."""
+    from vacancy_b200 import sharded
+    v, f = _mesh(seed=9, n=300)
+    whole = port.ply_text(v, f)
+    head_len = len(port.ply_text(v[:0], f[:0]).replace(b"vertex 0", b"vertex 300").replace(
+        b"face 0", b"face 150"))
+    body = whole[head_len:]
+    lines = body.split(b"\n")[:-1]
+    vlines, flines = [ln + b"\n" for ln in lines[:300]], [ln + b"\n" for ln in lines[300:]]
+    assert len(flines) == 150
+    parts = [(b"".join(vlines[:120]), b"".join(flines[:40])),
+             (b"".join(vlines[120:]), b"".join(flines[40:]))]
+    assert sharded.assemble_ply((300, 150), parts) == whole
