@@ -127,7 +127,8 @@ def reference_sample(cfg, n_views, planes):
     assert car.dims == (n, n, planes), car.dims
     cams = S.circle_cameras(V, size)
     pick = [int(round(i * V / n_views)) % V for i in range(n_views)]
-    threads = ref.threads() if kind == "reference" else (os.cpu_count() or 1)
+    # torch.distributed.run hands its workers OMP_NUM_THREADS=1: ask for every core explicitly
+    threads = ref.set_threads(-1)
     t_sdf = t_fuse = 0.0
     for vi in pick:
         mask = S.silhouette(cams[vi])
@@ -168,7 +169,7 @@ def run_reference_arm(args, cfg):
     if rank != 0:
         return
     total = args.steps + args.warmup
-    n_views = max(2, min(8, int(48 / max(total, 1))))
+    n_views = 8 if total <= 12 else max(4, int(96 / total))  # 8 sample views
     planes = 32
     vals, times = [], []
     last = None

@@ -147,7 +147,9 @@ int vcb_carve_sdfs(vcb_carver* c, int32_t n_views, const vcb_view* views,
 int vcb_carve_sdfs_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
                           const float* const* sdfs_dev);
 
-/* Free functions of voxel_carver.h:120-126 on HOST buffers, run on CUDA device `device`.
+/* Free functions of voxel_carver.h:120-126 on HOST buffers, run on CUDA device `device` (the
+ * caller's current device is restored before they return; they allocate and free their device
+ * buffers per call - hosts that transform many images should queue them on a carver instead).
  * DistanceTransformL1 (voxel_carver.cc:102-167) and MakeSignedDistanceField (:169-237). */
 int vcb_distance_transform_l1(int32_t device, const uint8_t* mask, int32_t width, int32_t height,
                               const int32_t roi_min[2], const int32_t roi_max[2], float* dist);
@@ -177,9 +179,10 @@ int vcb_signed_distance_to_color(int32_t device, const float* sdf, int32_t width
  * own arena has claimed the GPU's memory (a driver allocation may then fail, or fragment what is
  * left), or an acquisition loop that cannot afford the device-wide synchronisation an allocation
  * implies.  This variant therefore takes the mask and the result as DEVICE pointers supplied by the
- * caller, works on `cuda_stream` (a cudaStream_t, NULL = default stream) without waiting for it,
- * and keeps its intermediate storage (two int16 images and a bit-plane) in a fixed array inside
- * the library:
+ * caller, works on `cuda_stream` (a cudaStream_t created on `device`, NULL = that device's default
+ * stream) without waiting for it, and keeps its intermediate storage (two int16 images, the
+ * foreground bit-plane, the per-distance value table and two result cells) in a fixed array inside
+ * the library.  The caller's current device is the same after the call as before it.
  *   - limit: W32 * height <= 2048 * 2048 pixels, W32 = width rounded up to a multiple of 32;
  *     larger images are refused with VCB_ERR_INVALID (use vcb_make_signed_distance_field);
  *   - cost: every GPU that loads the library holds that array (16.75 MiB) until the process exits;
@@ -256,7 +259,11 @@ int vcb_extract_voxel_fill(vcb_carver* c, float* vertices, int32_t* faces);
 int vcb_extract_voxel_occupancy(vcb_carver* c, uint8_t* flags);
 
 /* Grid state of the owned slab to / from HOST buffers (the reference keeps the grid private,
- * voxel_carver.h:97; tests and checkpoints use these). Either pointer may be NULL. */
+ * voxel_carver.h:97; tests and checkpoints use these). Either pointer may be NULL.  Uploading both
+ * arrays of a grid a carver produced (update_num < 1 exactly where sdf == kVal) restores it fully;
+ * any other upload is accepted as arbitrary state, but marching cubes then needs update_num, which
+ * has no halo planes: on a z slab above the first vcb_extract_iso_begin returns
+ * VCB_ERR_UNSUPPORTED. */
 int vcb_download_grid(vcb_carver* c, float* sdf, int32_t* update_num);
 int vcb_upload_grid(vcb_carver* c, const float* sdf, const int32_t* update_num);
 /* DEVICE pointers to the owned slab's state (stream-ordered access only). */

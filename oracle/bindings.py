@@ -138,6 +138,11 @@ class RefLib:
     def threads(self):
         return int(self.L.ref_omp_threads())
 
+    def set_threads(self, n=-1):
+        """OpenMP threads of the reference's parallel loops; n < 0 = every core of the machine
+        (torch.distributed.run exports OMP_NUM_THREADS=1 to its workers)."""
+        return int(self.L.ref_set_omp_threads(int(n)))
+
     def distance_transform_l1(self, mask, roi=None):
         mask = np.ascontiguousarray(mask, dtype=np.uint8)
         h, w = mask.shape
@@ -338,6 +343,12 @@ class PortLib:
         L.vo_free.argtypes = [C.c_void_p]
         L.vo_mc_tables.argtypes = [c_int_p, c_int_p]
         self.kind = "port"
+
+    def set_threads(self, n=-1):
+        return int(self.L.vo_set_threads(int(n)))
+
+    def threads(self):
+        return int(self.L.vo_set_threads(0))
 
     def invalid_sdf(self):
         return np.float32(self.L.vo_invalid_sdf())

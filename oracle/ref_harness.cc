@@ -86,6 +86,19 @@ int ref_omp_threads() {
 #endif
 }
 
+// torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: the timed reference arm sets the
+// thread count explicitly (n < 0: every core of the machine, 0: only report).
+int ref_set_omp_threads(int n) {
+#ifdef _OPENMP
+  if (n < 0) n = omp_get_num_procs();
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
+
 void ref_set_quiet(int quiet) {
   vacancy::set_log_level(quiet ? vacancy::LogLevel::kNone
                                : vacancy::LogLevel::kVerbose);

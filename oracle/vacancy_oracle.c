@@ -11,6 +11,24 @@
 
 #include "mc_tables_packed.h"
 
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+/* threads of the one parallel loop (the fusion loop, like voxel_carver.cc:439-442); n < 0 = all
+ * cores, 0 = only report. torch.distributed.run exports OMP_NUM_THREADS=1, so the timed baseline
+ * sets the count itself. */
+int vo_set_threads(int n) {
+#ifdef _OPENMP
+  if (n < 0) n = omp_get_num_procs();
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
+
 static const uint64_t kTriPacked[256] = VCB_MC_TRI_PACKED_INIT;
 
 float vo_invalid_sdf(void) { return -FLT_MAX; } /* numeric_limits<float>::lowest() */

@@ -42,6 +42,7 @@ typedef struct vo_view {
   int32_t roi_min[2], roi_max[2]; /* inclusive */
 } vo_view;
 
+int vo_set_threads(int n); /* OpenMP threads of the fusion loop; n < 0 = all cores, 0 = report only */
 float vo_invalid_sdf(void); /* InvalidSdf::kVal voxel_carver.cc:100 */
 
 /* camera.cc:39-42 + Eigen 3.4.0 Transform::inverse(Affine) + cast<float> */

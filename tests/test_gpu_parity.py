@@ -63,6 +63,37 @@ def test_sdf2d_bunny_and_large(cuda_lib, port, bunny):
                           port.make_sdf(mask, None, True, trunc, 0.1))
 
 
+@pytest.mark.parametrize("shape,roi", [
+    ((64, 16384), None),                       # wide: width + height > 16000 -> strip-in-shared-memory column pass
+    ((16384, 64), (5, 3000, 60, 6100)),        # tall, ROI of 3101 rows (<= 3168): same kernel, partial ROI
+    ((5000, 12000), None),                     # 5000 rows > 3168: the three-sweep column pass
+    ((5000, 12000), (100, 200, 11000, 4900)),  # same, partial ROI (4701 rows)
+])
+def test_sdf2d_large_images_take_the_int32_column_passes(cuda_lib, port, shape, roi):
+    """Images with width + height > 16000 leave the packed 16-bit column pass (sdf_col_pack_kernel)
+    for sdf_col_smem_kernel (ROI height <= 3168) or sdf_col_kernel; both must stay bit-exact, with
+    columns that are all foreground / all background inside the ROI (no seed in the column)."""
+    h, w = shape
+    rng = np.random.default_rng(h * 7 + w)
+    yy, xx = np.mgrid[0:h, 0:w]
+    mask = (((yy * 3 + xx) // 97) % 2 == 0)
+    mask &= rng.random((h, w)) < 0.995        # a few isolated background pixels
+    mask[:, : w // 9] = True                   # all-foreground columns
+    mask[:, w - w // 11:] = False              # all-background columns
+    mask[h // 3: h // 3 + max(1, h // 50), :] = True  # all-foreground rows
+    mask = (mask * 255).astype(np.uint8)
+    rmin, rmax = (roi[:2], roi[2:]) if roi else (None, None)
+    assert bits_equal(distance_transform_l1(mask, rmin, rmax), port.distance_transform_l1(mask, roi))
+    for norm, trunc in ((True, False), (True, True), (False, True)):
+        got = make_signed_distance_field(mask, rmin, rmax, norm, trunc, 0.1)
+        want = port.make_sdf(mask, roi, norm, trunc, 0.1)
+        assert bits_equal(got, want), (shape, roi, norm, trunc)
+    # no pixel of the other class anywhere: +-FLT_MAX distances on both passes
+    full = np.full((h, w), 255, np.uint8)
+    assert bits_equal(make_signed_distance_field(full, rmin, rmax, True, False, 0.1),
+                      port.make_sdf(full, roi, True, False, 0.1))
+
+
 # ---- K1 + K2 + K3 on the bundled bunny (config 1) -----------------------------------------------
 @pytest.mark.parametrize("mode", ["max", "tsdf"])
 def test_bunny_view_by_view(cuda_lib, bunny, mode):
@@ -333,6 +364,36 @@ def test_cfg3_slab_weighted_against_compiled_reference(cuda_lib, ref):
     (gs, gn), (ws, wn) = car.download_grid(), rc.download()
     assert np.array_equal(gn, wn) and bits_equal(gs, ws)
     H.assert_mesh_equal(car.ExtractIsoSurface(), rc.extract_iso(), opt.bb_min, opt.bb_max)
+
+
+def test_cfg4_slab_all_360_views_against_compiled_reference(cuda_lib, ref):
+    """The benchmarked configuration itself (BASELINE.json config 4: 1024^2 planes, 2048^2 images,
+    the sphere scene, weighted TSDF with truncation, ALL 360 views so that the 256-update cap fires
+    and the fusion kernel's cap variant runs) on a 1024 x 1024 x 32 slab around z = 0, against the
+    UNMODIFIED reference: grid, update_num and the marching-cubes mesh of the slab, bit for bit.
+    The sphere looks the same from every camera of the circle (bench.py uses one rasterised mask
+    for all views, so does this test); the reference fuses the SDF image it computed itself."""
+    cfg = S.CONFIGS["cfg4"]
+    n, V, size, planes = cfg["grid"], cfg["views"], cfg["image"], 32
+    half = planes / n
+    res = float(np.float32(2.0) / np.float32(n))
+    opt = B.make_options((-1.0, -1.0, -half), (1.0, 1.0, half), res, update=1, truncation=True,
+                         band=0.1)
+    car, rc = make_carver(opt), ref.carver(opt)
+    assert car.dims == (n, n, planes) and rc.dims == (n, n, planes)
+    cams = S.circle_cameras(V, size)
+    mask = S.silhouette(cams[0])
+    assert np.array_equal(mask, S.silhouette(cams[V // 3]))  # what bench.py relies on
+    assert car.carve_batch(cams, [mask] * V)
+    ref_sdf = ref.make_sdf(mask, None, True, True, 0.1)
+    for c in cams:
+        rc.carve_sdf(H.to_oracle_camera(c), ref_sdf)
+    (gs, gn), (ws, wn) = car.download_grid(), rc.download()
+    assert int(wn.max()) == 256  # voxel_max_update_num = 255: a voxel takes at most 256 updates
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(car.ExtractIsoSurface(), rc.extract_iso(), opt.bb_min, opt.bb_max)
+    flags, cnt = car.occupancy(False)
+    assert cnt == int(((ws <= 0) & (wn >= 1)).sum())
 
 
 def test_sdf_color_map(cuda_lib, port, bunny):

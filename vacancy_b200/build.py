@@ -19,6 +19,9 @@ NVCC_FLAGS = [
 ]
 
 
+LINK_LIBS = ["-ldl"]  # NCCL is resolved with dlopen at run time (csrc/sharded.cu), never linked
+
+
 def _stale():
     if not os.path.exists(LIB):
         return True
@@ -32,12 +35,36 @@ def build_library(force=False, verbose=False):
     if not force and not _stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB]
-    cmd += [os.path.join(CSRC, s) for s in SOURCES]
-    r = subprocess.run(cmd, capture_output=True, text=True)
+    # the sources are compiled in parallel into objects, linked into a temporary file and moved
+    # into place, so that a repository snapshot taken meanwhile never sees a half-written library
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    compile_flags = [f for f in NVCC_FLAGS if f != "-shared"]
+    procs = []
+    for src in SOURCES:
+        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        cmd = [nvcc] + compile_flags + (["-Xptxas", "-v"] if verbose else []) + [
+            "-c", os.path.join(CSRC, src), "-o", obj]
+        procs.append((src, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE,
+                                                 stderr=subprocess.STDOUT, text=True)))
+    objs, failed, log = [], [], ""
+    for src, obj, pr in procs:
+        out, _ = pr.communicate()
+        log += out
+        objs.append(obj)
+        if pr.returncode != 0:
+            failed.append(src)
+    if failed:
+        sys.stderr.write(log)
+        raise RuntimeError("nvcc failed compiling " + ", ".join(failed))
+    tmp = LIB + ".tmp.%d" % os.getpid()
+    r = subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", tmp]
+                       + objs + LINK_LIBS, capture_output=True, text=True)
+    r.stdout = log + r.stdout
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
-        raise RuntimeError("nvcc failed building libvacancy_b200.so")
+        raise RuntimeError("nvcc failed linking libvacancy_b200.so")
+    os.replace(tmp, LIB)
     if verbose:
         sys.stderr.write(r.stdout + r.stderr)
     return LIB

@@ -16,7 +16,7 @@
 
 #include <mutex>
 
-#include "common.cuh"
+#include "carver_internal.cuh"
 
 using namespace vcb;
 
@@ -39,71 +39,9 @@ __global__ void __launch_bounds__(256) grid_reset_kernel(float4* __restrict__ sd
   if (t < (size_t)tail_un) un_tail[t] = 0;
 }
 
-struct TimedSpan {
-  cudaEvent_t a, b;
-  int stage;
-};
-
 }  // namespace
 
-constexpr int kMaxStageSets = kMaxViewsPerLaunch / kSdfSubBatch + 2;  // one launch ahead + 2
-constexpr size_t kStageBudgetBytes = (size_t)512 << 20;                // never more than this
-
-struct vcb_carver {
-  vcb_options opt;
-  int nx = 0, ny = 0, nz = 0;
-  int z_begin = 0, z_end = 0;
-  int halo = 0;
-  cudaStream_t stream = nullptr;
-  std::string err;
-
-  float* sdf_alloc = nullptr;  // halo planes first
-  float* sdf = nullptr;        // plane z_begin
-  int32_t* un = nullptr;
-  float *pos_x = nullptr, *pos_y = nullptr, *pos_z = nullptr;
-  std::vector<float> h_pos[3];
-  float2* wtab = nullptr;
-  int wtab_n = 0;
-  int64_t max_count = 0;  // upper bound of update_num over the grid (views fused / uploaded)
-  bool un_implied = true;  // update_num < 1  <=>  sdf == kVal (true unless a grid was uploaded)
-
-  // queued views
-  FuseParams fp;
-  int pending = 0;
-  Scratch pool;          // kMaxViewsPerLaunch image slots
-  size_t slot_floats = 0;
-  Scratch max_sdf;       // one float per slot
-  Scratch fuse_tabs;     // per-launch tables of the fusion kernel (fusion_table_bytes)
-  PlyText ply;           // ASCII PLY text of the last extracted mesh (vcb_ply_body_*)
-  Scratch tiles;         // 8x8-block flags per slot (tile_flag_bytes), see fusion.cu
-  size_t tile_slot_bytes = 0;
-  bool use_tiles = true;
-  // 2D SDF scratch
-  Scratch mask_stage, sdf_scratch, absmax;
-  // host masks are uploaded on a separate stream into a 2-deep ring of staging sets, so that the
-  // copy of one sub-batch overlaps the kernels of the previous ones
-  cudaStream_t copy_stream = nullptr;
-  // host masks travel through a ring of staging sets (kSdfSubBatch masks each) on their own copy
-  // stream; with enough sets the copies of the next 64 views run under the current fusion launch
-  cudaEvent_t ev_copied[kMaxStageSets] = {}, ev_consumed[kMaxStageSets] = {};
-  bool consumed_valid[kMaxStageSets] = {};
-  int stage_sets = 2;
-  unsigned stage_round = 0;
-  size_t sdf_pix = 0;      // mask staging bytes per view
-  size_t sdf_scr = 0;      // 2D-SDF scratch bytes per view
-
-  VoxelExtract vox;
-  IsoExtract iso;
-
-  bool timing = true;
-  std::vector<TimedSpan> spans;
-  float stage_ms[4] = {0, 0, 0, 0};
-  int64_t stage_launches[4] = {0, 0, 0, 0};
-};
-
-namespace {
-
-int flush_pending(vcb_carver* c);
+namespace vcb {  // helpers shared with sharded.cu (declared in carver_internal.cuh)
 
 int fail(vcb_carver* c, int code, const char* fmt, ...) {
   char buf[512];
@@ -118,14 +56,6 @@ int fail(vcb_carver* c, int code, const char* fmt, ...) {
   return code;
 }
 
-#define CU(c, call)                                                                          \
-  do {                                                                                       \
-    cudaError_t e_ = (call);                                                                 \
-    if (e_ != cudaSuccess)                                                                   \
-      return fail(c, VCB_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
-                  __LINE__);                                                                 \
-  } while (0)
-
 std::mutex g_init_mutex;
 bool g_tables_ready[64] = {false};
 
@@ -139,25 +69,6 @@ int use_device(vcb_carver* c, int device) {
   }
   return VCB_OK;
 }
-
-struct Span {
-  vcb_carver* c;
-  int stage;
-  cudaEvent_t a = nullptr, b = nullptr;
-  Span(vcb_carver* c_, int stage_) : c(c_), stage(stage_) {
-    if (c->timing) {
-      cudaEventCreate(&a);
-      cudaEventCreate(&b);
-      cudaEventRecord(a, c->stream);
-    }
-  }
-  ~Span() {
-    if (c->timing) {
-      cudaEventRecord(b, c->stream);
-      c->spans.push_back({a, b, stage});
-    }
-  }
-};
 
 void resolve_spans(vcb_carver* c) {
   for (auto& s : c->spans) {
@@ -359,6 +270,25 @@ int flush_pending(vcb_carver* c) {
   return VCB_OK;
 }
 
+int fuse_prepared(vcb_carver* c, int n, const vcb_view* views, const float* const* images,
+                  const uint32_t* const* tiles, const float* const* max_sdf) {
+  if (n < 0 || n > kMaxViewsPerLaunch) return fail(c, VCB_ERR_INVALID, "fuse_prepared: %d views", n);
+  int rc = flush_pending(c);
+  if (rc != VCB_OK || n == 0) return rc;
+  const bool flags = c->use_tiles && c->opt.sdf_interp == VCB_INTERP_BILINEAR;
+  for (int i = 0; i < n; i++) {
+    FuseView& f = c->fp.views[i];
+    fill_fuse_view(&f, views[i], images[i], max_sdf[i]);
+    if (flags && tiles && tiles[i]) {
+      f.tiles = tiles[i];
+      f.tile_words = tile_words_for(views[i].width);
+      f.tile_rows = tile_rows_for(views[i].height);
+    }
+  }
+  c->pending = n;
+  return flush_pending(c);
+}
+
 int ensure_pool(vcb_carver* c, size_t floats_per_image) {
   if (floats_per_image <= c->slot_floats && c->pool.ptr) return VCB_OK;
   int rc = flush_pending(c);
@@ -507,9 +437,6 @@ int carve_masks_impl(vcb_carver* c, int32_t n_views, const vcb_view* views,
   return VCB_OK;
 }
 
-}  // namespace
-
-namespace vcb {
 void set_global_error(const char* text) { g_last_error = text; }
 }  // namespace vcb
 
@@ -829,6 +756,7 @@ static int sdf_free_function(int32_t device, const uint8_t* mask, int32_t width,
   v.roi_max[1] = roi_max[1];
   int rc = check_view(nullptr, v);
   if (rc != VCB_OK) return rc;
+  DeviceGuard restore_callers_device;
   if ((rc = use_device(nullptr, device)) != VCB_OK) return rc;
   const size_t pix = (size_t)width * height;
   Scratch buf;
@@ -869,6 +797,7 @@ int vcb_signed_distance_to_color(int32_t device, const float* sdf, int32_t width
   if (width < 1 || height < 1) return fail(nullptr, VCB_ERR_INVALID, "empty image");
   if (!(min_negative_d < 0.0f) || !(0.0f < max_positive_d))  // the reference asserts these
     return fail(nullptr, VCB_ERR_INVALID, "need min_negative_d < 0 < max_positive_d");
+  DeviceGuard restore_callers_device;
   int rc = use_device(nullptr, device);
   if (rc != VCB_OK) return rc;
   const size_t n = (size_t)width * height;
@@ -915,6 +844,11 @@ int vcb_extract_iso_begin(vcb_carver* c, double iso_level, int32_t linear_interp
   if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
   int rc = vcb_flush(c);
   if (rc != VCB_OK) return rc;
+  if (!c->un_implied && c->halo != 0)
+    return fail(c, VCB_ERR_UNSUPPORTED,
+                "marching cubes on a z slab needs the uploaded grid to keep update_num < 1 <=> sdf == "
+                "kVal (update_num has no halo planes); upload sdf and update_num of a carved grid "
+                "together");
   {
     Span span(c, 3);
     cudaError_t e = iso_count(grid_desc(c), c->un_implied, iso_level, linear_interp, &c->iso,
@@ -1123,7 +1057,15 @@ int vcb_upload_grid(vcb_carver* c, const float* sdf, const int32_t* update_num) 
       if (update_num[i] > c->max_count) c->max_count = update_num[i];
     }
   }
-  c->un_implied = false;  // arbitrary state: marching cubes must read update_num itself
+  // A grid that a carver produced keeps "update_num < 1 <=> sdf == kVal" (a restored checkpoint
+  // does); only then may marching cubes go on reading sdf alone. Anything else is arbitrary state:
+  // marching cubes must read update_num itself (and, lacking halo planes of it, cannot run on a
+  // slab above the first - see vcb_extract_iso_begin).
+  bool consistent = sdf != nullptr && update_num != nullptr;
+  for (size_t i = 0; consistent && i < n; i++) {
+    consistent = (update_num[i] < 1) == (sdf[i] == kInvalidSdf);
+  }
+  if (!consistent) c->un_implied = false;
   return VCB_OK;
 }
 

@@ -125,6 +125,14 @@ struct GridDesc {
   float resolution;
 };
 
+// Entry points that are not tied to a carver (the free functions) switch to the device they were
+// asked to run on and put the caller's current device back when they return.
+struct DeviceGuard {
+  int prev = -1;
+  DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 struct Scratch {  // grow-only device buffer
   void* ptr = nullptr;
   size_t bytes = 0;

@@ -144,6 +144,7 @@ extern "C" int vcb_ply_format(int32_t device, const float* vertices, int64_t n_v
   }
   size_t header = 0;
   vcb_ply_header(n_vertices, n_faces, nullptr, 0, &header);
+  DeviceGuard restore_callers_device;
   cudaError_t e = cudaSetDevice(device);
   float* dv = nullptr;
   int32_t* df = nullptr;

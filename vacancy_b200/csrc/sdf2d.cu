@@ -12,14 +12,22 @@
 //   sdf_row_kernel : one warp per ROI row, one lane per 32-pixel word: warp max/min scans carry the
 //                    nearest foreground / background pixel across words, clz/ffs resolve it inside a
 //                    word.  Output: signed row distance (fg negative, bg positive), kRowInf = none.
-//   sdf_col_kernel : one block per 32 columns x 8 row segments; prefix-min of (g(y') - y') and
-//                    suffix-min of (g(y') + y') per segment, carries exchanged through shared memory,
-//                    for both polarities at once.  Output: signed L1 distance + max |D| (atomic).
-//   sdf_finalize_kernel : int -> float, whole-image min/max normalisation (:205-222), truncation
-//                    (:225-236), zeros outside the ROI (:104), and the image maximum that
-//                    Carve needs for UpdateOutsideImage::kMax (:436).
-// Algorithmic bytes: 1 B (mask) + 4 B (float SDF) per pixel; the int16 scratch adds 8 B/pixel of
-// L2-resident traffic (views are processed kSdfSubBatch at a time to keep it there).
+//   sdf_col_pack_kernel : the column pass of every image with width + height <= 16000 (all the
+//                    benchmark configurations): two columns per thread on the packed 16-bit SIMD
+//                    integer instructions (VIADDMNMX.S16x2), 16 row segments per block; a forward
+//                    sweep per segment without carries, segment summaries through shared memory, a
+//                    backward sweep with both carries; both polarities at once.  Output: signed L1
+//                    distance (int16) + max |D| (atomic).
+//   sdf_col_smem_kernel / sdf_col_kernel : the same pass for larger images (strip staged in shared
+//                    memory / three sweeps over global memory), int32 arithmetic.
+//   sdf_lut_kernel : the float value of a pixel depends on its integer distance only, so int ->
+//                    float, min/max normalisation (:205-222) and truncation (:225-236) run once per
+//                    possible distance into a per-view table.
+//   sdf_finalize_kernel : table gather per pixel, zeros outside the ROI (:104), the image maximum
+//                    that Carve needs for UpdateOutsideImage::kMax (:436) and the 8x8-block flags
+//                    the fusion kernel classifies voxel tiles with.
+// Algorithmic bytes: 1 B (mask) + 4 B (float SDF) per pixel; the int16 scratch adds L2-resident
+// traffic (views are processed kSdfSubBatch at a time to keep it there).
 #include <float.h>
 #include <stdio.h>
 
@@ -834,8 +842,9 @@ void launch_image_max(const float* image, int64_t n, float* max_out, cudaStream_
 // ------------------------------------------------------------------------------------------------
 // vcb_make_signed_distance_field_noalloc: the 2D SDF of one mask without a single allocation.
 //
-// The kernels above need 4 bytes of scratch per pixel (two int16 images), a value table and a small
-// descriptor block.  Here that scratch is this fixed array, part of the library image: every GPU
+// The kernels above need 4 bytes of scratch per pixel (two int16 images), one bit per pixel (the
+// foreground bit-plane), a value table (one float per possible distance) and two cells (the
+// largest |distance| and the image maximum).  Here all of it is this fixed array, part of the library image: every GPU
 // that loads libvacancy_b200.so carries it (16.75 MiB) until the process exits, and images of more
 // than kNoAllocMaxPixels pixels (width rounded up to a multiple of 32) are refused.  All calls
 // share the one array.
@@ -888,6 +897,7 @@ extern "C" int vcb_make_signed_distance_field_noalloc(
     set_global_error("vcb_make_signed_distance_field_noalloc: device ordinal out of range");
     return VCB_ERR_INVALID;
   }
+  DeviceGuard restore_callers_device;  // the caller's current device is put back on return
   cudaError_t e = cudaSetDevice(device);
   unsigned char* scratch = nullptr;
   if (e == cudaSuccess) {
