@@ -213,9 +213,9 @@ def run_ours(args, cfg):
     n, V, size = cfg["grid"], cfg["views"], cfg["image"]
     hbm_peak, peak_src, _ = load_peaks()
 
-    stream = torch.cuda.Stream()
-    car = sharded.ShardedCarver(S.grid_option(n, weighted=cfg["weighted"]), rank, world, local,
-                                stream=stream)
+    car = sharded.ShardedCarver(S.grid_option(n, weighted=cfg["weighted"]), rank, world, local)
+    # the engine orders a slab's reset / fusion / extraction on its own main stream: time on it
+    stream = torch.cuda.ExternalStream(car.main_stream(0), device=torch.device("cuda", local))
     cams = S.circle_cameras(V, size)
     # the sphere at the origin looks the same from every camera on the circle: rasterise once
     mask0 = S.silhouette(cams[0])
@@ -236,13 +236,18 @@ def run_ours(args, cfg):
         return car.extract_iso_counts(0.0, True)
 
     host_np = [host_masks[i].numpy() for i in range(V)]
+    e2e_mesh = {}
 
     def step_e2e():
+        # the call a host makes: pinned HOST masks in, the WHOLE mesh on one host out (rank 0's;
+        # the other ranks send their part over NVLink inside vcb_sharded_extract_iso_fill)
         car.reset()
         car.carve_host_masks(cams, host_np)
         total = car.extract_iso_counts(0.0, True)
-        v, f = car.slab.mesh_host(*car._counts)  # this rank's part of the mesh, global vertex ids
-        return total[0], total[1], v.nbytes + f.nbytes
+        mesh = car.mesh_host(receive=rank == 0)
+        if mesh is not None:
+            e2e_mesh["v"], e2e_mesh["f"] = mesh
+        return total[0], total[1], (total[0] + total[1]) * 12 if rank == 0 else 0
 
     def timed(fn, steps):
         barrier()
@@ -294,6 +299,22 @@ def run_ours(args, cfg):
     ms_e2e = ms_e2e_total / e2e_steps
     # the host path must produce the mesh of the resident path (same global counts on every rank)
     assert (int(e2e_out[0]), int(e2e_out[1])) == (int(counts[0]), int(counts[1])), (e2e_out, counts)
+    # ... and, by CONTENT, the mesh a single GPU produces: sha256 of the vertex and face buffers
+    # gathered on rank 0 against the value committed from a 1-GPU run (tests/golden/bench_mesh_sha.json)
+    mesh_sha = mesh_sha_ok = None
+    if rank == 0:
+        import hashlib
+        hsh = hashlib.sha256()
+        hsh.update(np.ascontiguousarray(e2e_mesh["v"]).tobytes())
+        hsh.update(np.ascontiguousarray(e2e_mesh["f"]).tobytes())
+        mesh_sha = hsh.hexdigest()
+        gpath = os.path.join(ROOT, "tests", "golden", "bench_mesh_sha.json")
+        if os.path.exists(gpath):
+            with open(gpath) as f:
+                want = json.load(f).get(cfg["name"])
+            if want:
+                mesh_sha_ok = want["sha256"] == mesh_sha
+                assert mesh_sha_ok, "mesh differs from the 1-GPU golden: %s != %s" % (mesh_sha, want["sha256"])
 
     nvox = float(n) ** 3
     updates = nvox * V
@@ -335,7 +356,9 @@ def run_ours(args, cfg):
         "e2e": {"value": updates / (ms_e2e * 1e-3) / 1e9, "unit": "Gvoxel-view/s",
                 "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(V * size * size),
                 "d2h_bytes_per_step": int(e2e_out[2]), "steps": e2e_steps,
-                "api": "VoxelCarver.carve_batch(host pinned masks) + ExtractIsoSurface -> host mesh"},
+                "api": "vcb_sharded_carve_masks(host pinned masks; each rank uploads the views it "
+                       "owns) + vcb_sharded_extract_iso_count/_fill -> the whole mesh on rank 0's host",
+                "mesh_sha256": mesh_sha, "mesh_equals_1gpu_golden": mesh_sha_ok},
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "roofline": {"kernel": "fuse_kernel", "bound": "hbm", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,

@@ -253,7 +253,9 @@ int vcb_halo_device(vcb_carver* c, float** halo_dev, int32_t* n_planes);
 /* ExtractVoxel(mesh, inside_empty), voxel_carver.cc:530-538 -> extract_voxel.cc:258-317.
  * _count classifies the voxels and returns how many cubes will be emitted (24 vertices and 12
  * faces each); _fill writes them to HOST buffers in the reference's raster order;
- * _occupancy writes one byte per owned voxel (1 = emitted) to a HOST buffer instead. */
+ * _occupancy writes one byte per owned voxel (1 = emitted) to a HOST buffer instead.
+ * On a z slab above the first, inside_empty looks at the plane below the slab: fill the halo
+ * (vcb_halo_device) from the lower slab first, as for marching cubes (vcb_sharded_* does). */
 int vcb_extract_voxel_count(vcb_carver* c, int32_t inside_empty, int64_t* n_voxels);
 int vcb_extract_voxel_fill(vcb_carver* c, float* vertices, int32_t* faces);
 int vcb_extract_voxel_occupancy(vcb_carver* c, uint8_t* flags);
@@ -268,6 +270,82 @@ int vcb_download_grid(vcb_carver* c, float* sdf, int32_t* update_num);
 int vcb_upload_grid(vcb_carver* c, const float* sdf, const int32_t* update_num);
 /* DEVICE pointers to the owned slab's state (stream-ordered access only). */
 int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev);
+
+/* ---- one grid across several GPUs (z slabs) ---------------------------------------------------
+ * No counterpart in the reference, which is single-process and single-device: a vcb_sharded stands
+ * where ONE vacancy::VoxelCarver stands (voxel_carver.h:95-118) and gives the same results - the
+ * slabs together hold exactly the grid, and extract exactly the mesh (vertex numbering and face
+ * order of marching_cubes.cc:199-218 over the whole grid), of a single carver.  GPU r owns the z
+ * planes [z_bounds[r], z_bounds[r+1]).  Per chunk of <= 64 views, view i is transformed to its 2D
+ * SDF (voxel_carver.cc:169-237) by GPU i mod N only; the float images are all-gathered over NVLink
+ * and every GPU fuses all of them into its slab (voxel_carver.cc:415-496), the next chunk's
+ * transforms and gathers running under the current chunk's fusion.  Marching cubes exchanges the
+ * two sdf planes below each slab, the per-slab counts and one plane of vertex ids.
+ *
+ *   vcb_sharded_create        ONE process drives `n_devices` GPUs (a device may be listed more than
+ *                             once: "virtual slabs", used by the single-GPU tests); exchanges are
+ *                             peer copies between the devices.
+ *   vcb_sharded_create_rank   one process per GPU (`rank` of `world`): exchanges are NCCL calls on
+ *                             a communicator built from the 128-byte id that rank 0 obtains from
+ *                             vcb_sharded_unique_id and the launcher hands to every rank.  Every
+ *                             rank makes the same calls with the same views (masks may be NULL-free
+ *                             copies of the same data; only the owner of a view reads its mask).
+ *                             libnccl.so.2 is loaded on first use, never linked.
+ *   z_bounds                  NULL (equal slabs) or world + 1 plane indices from 0 to nz; every slab
+ *                             holds at least 2 planes.  vcb_sharded_repartition re-creates the slabs
+ *                             on other boundaries (grid state is discarded, like Init()). */
+#define VCB_UNIQUE_ID_BYTES 128
+typedef struct vcb_sharded vcb_sharded;
+int vcb_sharded_create(const vcb_options* opt, const int32_t* devices, int32_t n_devices,
+                       const int32_t* z_bounds, vcb_sharded** out);
+int vcb_sharded_unique_id(void* id128);
+int vcb_sharded_create_rank(const vcb_options* opt, int32_t device, int32_t rank, int32_t world,
+                            const void* id128, const int32_t* z_bounds, vcb_sharded** out);
+void vcb_sharded_destroy(vcb_sharded* s);
+const char* vcb_sharded_last_error(const vcb_sharded* s);
+int vcb_sharded_info(const vcb_sharded* s, int32_t* world, int32_t* n_local, int32_t dims3[3]);
+int vcb_sharded_bounds(const vcb_sharded* s, int32_t* z_bounds /* world + 1 */);
+int vcb_sharded_repartition(vcb_sharded* s, const int32_t* z_bounds);
+/* i-th slab held by THIS process (0 <= i < n_local) and its rank: the carver handle serves
+ * vcb_download_grid, vcb_grid_device, vcb_ply_body_*, ... on that slab; do not carve through it. */
+int vcb_sharded_local(vcb_sharded* s, int32_t i, vcb_carver** carver, int32_t* rank);
+/* The CUDA stream (a cudaStream_t) that orders the i-th local slab's reset, fusion and extraction
+ * work - for hosts that time the engine with events or chain their own work behind it. */
+int vcb_sharded_stream(vcb_sharded* s, int32_t i, void** main_stream);
+/* Init() again (voxel_carver.cc:390-391): every slab back to sdf = kVal, update_num = 0. */
+int vcb_sharded_reset(vcb_sharded* s);
+/* Carve for n views, as vcb_carve_masks / vcb_carve_masks_device (voxel_carver.cc:394-413).  HOST
+ * masks are read during the call only, and only the owner's process / device uploads a mask;
+ * DEVICE masks must be readable from the owning GPU (single process: any local device's memory
+ * with peer access) and stay valid until the streams have passed this call.  A view with a
+ * non-NULL sdf_out entry is fused in a launch of its own so that its 2D SDF can be returned. */
+int vcb_sharded_carve_masks(vcb_sharded* s, int32_t n_views, const vcb_view* views,
+                            const uint8_t* const* masks, float* const* sdf_out);
+int vcb_sharded_carve_masks_device(vcb_sharded* s, int32_t n_views, const vcb_view* views,
+                                   const uint8_t* const* masks_dev, float* const* sdf_out_dev);
+/* Carve(camera, roi, sdf) with ready-made HOST float SDF images (voxel_carver.cc:415-496): every
+ * slab fuses them as given. */
+int vcb_sharded_carve_sdfs(vcb_sharded* s, int32_t n_views, const vcb_view* views,
+                           const float* const* sdfs);
+int vcb_sharded_flush(vcb_sharded* s);
+int vcb_sharded_synchronize(vcb_sharded* s);
+/* ExtractIsoSurface over the whole grid (voxel_carver.cc:540-543): _count returns the GLOBAL sizes
+ * on every rank; _fill copies the WHOLE mesh into host buffers - in a single process every device
+ * writes its part of them, with one process per GPU the parts are sent to rank 0, whose buffers
+ * receive the mesh (the other ranks pass NULL and only send).  _local_mesh: the part of slab i that
+ * stays on its device (vcb_extract_iso_device on the slab's carver), ids already global. */
+int vcb_sharded_extract_iso_count(vcb_sharded* s, double iso_level, int32_t linear_interp,
+                                  int64_t* n_vertices, int64_t* n_faces);
+int vcb_sharded_extract_iso_fill(vcb_sharded* s, float* vertices, int32_t* faces);
+int vcb_sharded_local_mesh(vcb_sharded* s, int32_t i, int64_t* n_vertices, int64_t* n_faces,
+                           int64_t* vertex_offset, int64_t* face_offset);
+/* ExtractVoxel over the whole grid (voxel_carver.cc:530-538, extract_voxel.cc:258-317), inside_empty
+ * included (the surface test reads the halo plane below each slab): global cube count, then - single
+ * process only - all cubes in the reference's raster order into host buffers. */
+int vcb_sharded_extract_voxel_count(vcb_sharded* s, int32_t inside_empty, int64_t* n_voxels);
+int vcb_sharded_extract_voxel_fill(vcb_sharded* s, float* vertices, int32_t* faces);
+/* vcb_stage_times of the i-th local slab (its 2D SDF share runs on a side stream, included). */
+int vcb_sharded_stage_times(vcb_sharded* s, int32_t i, float ms[4], int64_t launches[4]);
 
 /* Device time in milliseconds spent by this carver's kernels since the last call, by stage:
  * [0] 2D SDF, [1] fusion, [2] ExtractVoxel, [3] marching cubes; launches[4] likewise counts kernel

@@ -1,0 +1,137 @@
+"""GPU tests of the z-slab engine behind vcb_sharded_* (csrc/sharded.cu) on ONE GPU: the device is
+listed several times, so every slab, every split of the 2D SDF work, every gather and every
+halo / count / vertex-id exchange of the multi-GPU algorithm runs - with peer copies that happen to
+stay on one device.  The checker is the CPU oracle on the whole, unsharded grid: the slabs together
+must reproduce its grid, its occupancy and its mesh bit for bit (same vertex numbering, same face
+order).  The NCCL transport of the one-process-per-GPU mode shares all of this code except the
+exchange calls; bench.py checks it by content (mesh sha256) on real multi-GPU runs."""
+import numpy as np
+import pytest
+
+from oracle import bindings as B
+from tests import helpers as H
+from vacancy_b200 import VoxelCarver, sharded
+from vacancy_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+
+def bits_equal(a, b):
+    return a.shape == b.shape and np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+def scene(n=96, views=70, size=256, weighted=True, tilt=0.3):
+    o = S.grid_option(n, weighted=weighted)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=int(weighted),
+                         truncation=weighted, band=0.1)
+    cams = S.circle_cameras(views, size, tilt=tilt)
+    masks = [S.silhouette(c, S.DUMBBELL) for c in cams]
+    return o, opt, cams, masks
+
+
+def oracle_carve(port, opt, cams, masks):
+    orc = port.carver(opt)
+    for c, m in zip(cams, masks):
+        orc.carve_mask(H.to_oracle_camera(c), m)
+    return orc
+
+
+@pytest.mark.parametrize("n_slabs", [1, 2, 3, 8])
+def test_engine_equals_oracle_more_views_than_one_chunk(cuda_lib, port, n_slabs):
+    """70 views = two fusion launches (the second chunk's transforms run under the first chunk's
+    fusion), slab counts that do and do not divide the chunk of 64, host masks."""
+    o, opt, cams, masks = scene()
+    orc = oracle_carve(port, opt, cams, masks)
+    eng = sharded.LocalSlabs(o, n_slabs)
+    assert eng.carve_batch(cams, masks)
+    gs, gn = eng.download_grid()
+    ws, wn = orc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    for iso, interp in ((0.0, True), (0.02, False)):
+        H.assert_mesh_equal(eng.extract_iso(iso, interp), orc.extract_iso(iso, interp), o.bb_min,
+                            o.bb_max)
+    # a second pass after reset reuses both halves of every pool
+    eng.reset()
+    assert eng.carve_batch(cams[:10], masks[:10])
+    orc2 = oracle_carve(port, opt, cams[:10], masks[:10])
+    gs, gn = eng.download_grid()
+    ws, wn = orc2.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+
+
+def test_engine_view_by_view_with_sdf_out_and_mixed_sizes(cuda_lib, port):
+    """Views arriving one per call (the reference's Carve(camera, mask, &sdf) pattern), some asking
+    for their 2D SDF back, with image sizes that grow mid-stream (the pools are re-allocated), on
+    unequal slabs."""
+    import ctypes as C
+    from vacancy_b200 import capi
+    o = S.grid_option(64, weighted=True)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True, band=0.1)
+    eng = sharded.LocalSlabs(o, 3, ranges=[(0, 10), (10, 40), (40, 64)])
+    orc = port.carver(opt)
+    sizes = [128] * 5 + [200] * 4 + [160] * 3
+    for i, size in enumerate(sizes):
+        cam = S.circle_cameras(len(sizes), size, tilt=0.25)[i]
+        mask = S.silhouette(cam, S.DUMBBELL)
+        view = sharded.make_view(cam, size, size)
+        want_sdf = i % 3 == 0
+        out = np.full((size, size), np.nan, np.float32) if want_sdf else None
+        views = (capi.View * 1)(view)
+        masks = (C.c_void_p * 1)(mask.ctypes.data)
+        outs = (C.c_void_p * 1)(out.ctypes.data) if want_sdf else None
+        eng._check(eng._lib.vcb_sharded_carve_masks(eng._h, 1, views, masks, outs))
+        orc.carve_mask(H.to_oracle_camera(cam), mask)
+        if want_sdf:
+            assert bits_equal(out, port.make_sdf(mask, None, True, True, 0.1))
+    gs, gn = eng.download_grid()
+    ws, wn = orc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(eng.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)
+
+
+@pytest.mark.parametrize("n_slabs", [2, 5])
+def test_engine_extract_voxel_and_inside_empty_across_slabs(cuda_lib, port, n_slabs):
+    """ExtractVoxel over slabs: the default rule and the inside_empty surface rule (which looks one
+    plane down, i.e. into the halo below every slab) give the oracle's emitted set; the cube mesh
+    equals the one a single carver writes (numbered over the whole grid)."""
+    o, opt, cams, masks = scene(n=64, views=9, size=192, weighted=False)
+    orc = oracle_carve(port, opt, cams, masks)
+    eng = sharded.LocalSlabs(o, n_slabs)
+    assert eng.carve_batch(cams, masks)
+    one = VoxelCarver(o)
+    assert one.Init() and one.carve_batch(cams, masks)
+    for inside_empty in (False, True):
+        flags, n = eng.occupancy(inside_empty)
+        wflags, wn = orc.occupancy(inside_empty)
+        assert n == wn and np.array_equal(flags, wflags), inside_empty
+        gv, gf = eng.extract_voxel(inside_empty)
+        sv, sf = one.ExtractVoxel(inside_empty)
+        assert np.array_equal(gf, sf) and bits_equal(gv, sv)
+
+
+def test_engine_repartition_and_errors(cuda_lib, port):
+    o, opt, cams, masks = scene(n=64, views=6, size=128)
+    orc = oracle_carve(port, opt, cams, masks)
+    eng = sharded.LocalSlabs(o, 4)
+    assert eng.ranges == [(0, 16), (16, 32), (32, 48), (48, 64)]
+    assert eng.carve_batch(cams[:2], masks[:2])
+    import ctypes as C
+    new = [(0, 8), (8, 40), (40, 42), (42, 64)]
+    eng.slabs = []
+    eng._check(eng._lib.vcb_sharded_repartition(eng._h, sharded._bounds_array(new)))
+    eng._refresh()
+    assert eng.ranges == new
+    assert eng.carve_batch(cams, masks)  # the grid started over, like Init()
+    gs, gn = eng.download_grid()
+    ws, wn = orc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(eng.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)
+    # a slab of one plane cannot serve its neighbour's halo
+    bad = (C.c_int32 * 5)(0, 1, 32, 48, 64)
+    assert eng._lib.vcb_sharded_repartition(eng._h, bad) == -1
+    assert b"at least 2" in eng._lib.vcb_sharded_last_error(eng._h)
+    # fill before count
+    eng2 = sharded.LocalSlabs(o, 2)
+    assert eng2._lib.vcb_sharded_extract_iso_fill(eng2._h, None, None) == -3
+    with pytest.raises(Exception):
+        sharded.LocalSlabs(o, 2, devices=[0, 99])

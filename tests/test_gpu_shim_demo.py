@@ -26,13 +26,13 @@ def read_ply(path):
     return verts.reshape(-1, 3), faces.reshape(-1, 3), lines
 
 
-def run_demo(binary, workdir):
+def run_demo(binary, workdir, env=None):
     os.makedirs(os.path.join(workdir, "bin"))
     shutil.copytree(os.path.join(REF_DIR, "data"), os.path.join(workdir, "data"))
     for f in os.listdir(os.path.join(workdir, "data")):
         os.chmod(os.path.join(workdir, "data", f), 0o644)
     r = subprocess.run([binary], cwd=os.path.join(workdir, "bin"), capture_output=True, text=True,
-                       timeout=600)
+                       timeout=600, env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     return os.path.join(workdir, "data")
 
@@ -59,6 +59,24 @@ def test_examples_cc_unchanged_through_shim(tmp_path):
     assert np.abs(va - vb).max() <= 1e-5 * diag
 
 
+def test_examples_cc_unchanged_on_several_slabs(tmp_path):
+    """The same unchanged demo with VACANCY_B200_DEVICES=0,0,0: the shim then carves the ONE grid as
+    three z slabs through vcb_sharded_* (here three virtual slabs on the one GPU of the test box -
+    a host with more GPUs lists them instead) and every file must still be byte-identical to what the
+    single-carver run writes: meshes, per-view SDF images, and the voxel cubes."""
+    ours = os.path.join(REF_DIR, "examples_b200")
+    if not os.path.exists(ours):
+        pytest.skip("prebuilt demo binary not present under oracle/_ref")
+    a = run_demo(ours, str(tmp_path / "slabs"), env={"VACANCY_B200_DEVICES": "0,0,0"})
+    b = run_demo(ours, str(tmp_path / "single"))
+    names = ["%s_%05d.%s" % (k, i, e) for i in range(6)
+             for k, e in (("surface", "ply"), ("surface_nointerp", "ply"), ("sdf", "png"),
+                          ("voxel", "ply"))]
+    for name in names:
+        with open(os.path.join(a, name), "rb") as f1, open(os.path.join(b, name), "rb") as f2:
+            assert f1.read() == f2.read(), name
+
+
 def test_pointer_batch_overload(tmp_path):
     """vacancy_b200::CarveBatch (include/vacancy_b200_batch.h): all six bunny views in one call from
     C++ host code give the reference's final mesh and cube counts."""
@@ -75,4 +93,14 @@ def test_pointer_batch_overload(tmp_path):
     assert want.startswith(b"ply\nformat ascii 1.0\nelement vertex 8672\n")
     for name in ("surface_gpu_writer.ply", "surface_gpu_direct.ply"):
         with open(tmp_path / name, "rb") as f:
+            assert f.read() == want, name
+    # the same host program on two z slabs (ExtractIsoSurfaceToPly assembles the slabs' text blocks)
+    out2 = tmp_path / "slabs"
+    out2.mkdir()
+    r = subprocess.run([demo, os.path.join(REF_DIR, "data") + "/", str(out2)], capture_output=True,
+                       text=True, timeout=300, env=dict(os.environ, VACANCY_B200_DEVICES="0,0"))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.split() == ["8672", "17270", "28475"]
+    for name in ("surface_reference_writer.ply", "surface_gpu_writer.ply", "surface_gpu_direct.ply"):
+        with open(out2 / name, "rb") as f:
             assert f.read() == want, name

@@ -61,7 +61,10 @@ def _worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     off, total = sharded.gather_offsets(100 * (rank + 1), 7 + rank, world)
-    q.put((rank, off.tolist(), total.tolist()))
+    # the NCCL unique id the one-process-per-GPU engine is built from: made on rank 0 by the library,
+    # carried to the other ranks by torch.distributed (the only job torch has on that path)
+    uid = sharded.broadcast_unique_id(rank, world)
+    q.put((rank, off.tolist(), total.tolist(), uid))
     dist.destroy_process_group()
 
 
@@ -79,5 +82,6 @@ def test_count_exchange_world2_gloo():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, off, total in res:
+    for rank, off, total, uid in res:
         assert off == [[0, 0], [100, 7]] and total == [300, 15]
+    assert len(res[0][3]) == 128 and res[0][3] == res[1][3] and any(res[0][3])

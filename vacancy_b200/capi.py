@@ -50,7 +50,15 @@ EXPORTS = [
     "vcb_extract_voxel_count", "vcb_extract_voxel_fill", "vcb_extract_voxel_occupancy",
     "vcb_download_grid", "vcb_upload_grid", "vcb_grid_device", "vcb_stage_times",
     "vcb_ply_header", "vcb_ply_body_size", "vcb_ply_body_fill", "vcb_ply_format",
+    "vcb_sharded_create", "vcb_sharded_unique_id", "vcb_sharded_create_rank", "vcb_sharded_destroy",
+    "vcb_sharded_last_error", "vcb_sharded_info", "vcb_sharded_bounds", "vcb_sharded_repartition",
+    "vcb_sharded_local", "vcb_sharded_stream", "vcb_sharded_reset", "vcb_sharded_carve_masks",
+    "vcb_sharded_carve_masks_device", "vcb_sharded_carve_sdfs", "vcb_sharded_flush", "vcb_sharded_synchronize",
+    "vcb_sharded_extract_iso_count", "vcb_sharded_extract_iso_fill", "vcb_sharded_local_mesh",
+    "vcb_sharded_extract_voxel_count", "vcb_sharded_extract_voxel_fill", "vcb_sharded_stage_times",
 ]
+
+UNIQUE_ID_BYTES = 128  # VCB_UNIQUE_ID_BYTES
 
 _lib = None
 
@@ -119,6 +127,30 @@ def load_library(path=LIB_PATH):
     L.vcb_ply_body_size.argtypes = [vp, szp, szp]
     L.vcb_ply_body_fill.argtypes = [vp, vp, vp]
     L.vcb_ply_format.argtypes = [i32, fp, i64, ip, i64, vp, C.c_size_t, szp]
+    L.vcb_sharded_create.argtypes = [C.POINTER(Options), ip, i32, ip, C.POINTER(vp)]
+    L.vcb_sharded_unique_id.argtypes = [vp]
+    L.vcb_sharded_create_rank.argtypes = [C.POINTER(Options), i32, i32, i32, vp, ip, C.POINTER(vp)]
+    L.vcb_sharded_destroy.argtypes = [vp]
+    L.vcb_sharded_destroy.restype = None
+    L.vcb_sharded_last_error.argtypes = [vp]
+    L.vcb_sharded_last_error.restype = C.c_char_p
+    L.vcb_sharded_info.argtypes = [vp, ip, ip, ip]
+    L.vcb_sharded_bounds.argtypes = [vp, ip]
+    L.vcb_sharded_repartition.argtypes = [vp, ip]
+    L.vcb_sharded_local.argtypes = [vp, i32, C.POINTER(vp), ip]
+    L.vcb_sharded_stream.argtypes = [vp, i32, C.POINTER(vp)]
+    L.vcb_sharded_reset.argtypes = [vp]
+    L.vcb_sharded_carve_masks.argtypes = [vp, i32, C.POINTER(View), pp, pp]
+    L.vcb_sharded_carve_masks_device.argtypes = [vp, i32, C.POINTER(View), pp, pp]
+    L.vcb_sharded_carve_sdfs.argtypes = [vp, i32, C.POINTER(View), pp]
+    L.vcb_sharded_flush.argtypes = [vp]
+    L.vcb_sharded_synchronize.argtypes = [vp]
+    L.vcb_sharded_extract_iso_count.argtypes = [vp, C.c_double, i32, C.POINTER(i64), C.POINTER(i64)]
+    L.vcb_sharded_extract_iso_fill.argtypes = [vp, fp, ip]
+    L.vcb_sharded_local_mesh.argtypes = [vp, i32] + [C.POINTER(i64)] * 4
+    L.vcb_sharded_extract_voxel_count.argtypes = [vp, i32, C.POINTER(i64)]
+    L.vcb_sharded_extract_voxel_fill.argtypes = [vp, fp, ip]
+    L.vcb_sharded_stage_times.argtypes = [vp, i32, fp, C.POINTER(i64)]
     _lib = L
     return L
 
@@ -126,4 +158,10 @@ def load_library(path=LIB_PATH):
 def check(L, handle, rc):
     if rc != 0:
         text = L.vcb_last_error(handle)
+        raise VcbError(rc, text.decode() if text else "")
+
+
+def check_sharded(L, handle, rc):
+    if rc != 0:
+        text = L.vcb_sharded_last_error(handle)
         raise VcbError(rc, text.decode() if text else "")

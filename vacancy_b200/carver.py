@@ -199,13 +199,22 @@ class VoxelCarver:
         self._z_range = z_range
         self.last_error = ""
 
+    @classmethod
+    def borrowed(cls, handle, option=None):
+        """Wraps a carver handle that somebody else owns (a slab of a ShardedCarver): the state
+        access / extraction helpers work on it, close() leaves it alone."""
+        self = cls(option)
+        self._h, self._owned = C.c_void_p(handle), False
+        self._query_geometry()
+        return self
+
     def __del__(self):
         self.close()
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and getattr(self, "_owned", True):
             self._lib.vcb_destroy(self._h)
-            self._h = None
+        self._h = None
 
     def set_option(self, option):  # voxel_carver.cc:373
         self._option = option
@@ -223,6 +232,11 @@ class VoxelCarver:
                 raise capi.VcbError(rc, self.last_error)
             return False
         self._h = h
+        self._owned = True
+        self._query_geometry()
+        return True
+
+    def _query_geometry(self):
         d = (C.c_int32 * 3)()
         self._lib.vcb_grid_dims(self._h, d)
         self.dims = (d[0], d[1], d[2])
@@ -230,7 +244,6 @@ class VoxelCarver:
         self._lib.vcb_slab_range(self._h, C.byref(z0), C.byref(z1))
         self.z_range = (z0.value, z1.value)
         self.slab_voxels = self.dims[0] * self.dims[1] * (z1.value - z0.value)
-        return True
 
     def _check(self, rc):
         capi.check(self._lib, self._h, rc)

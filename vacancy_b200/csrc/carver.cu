@@ -994,8 +994,10 @@ int vcb_extract_voxel_count(vcb_carver* c, int32_t inside_empty, int64_t* n_voxe
   if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
   int rc = vcb_flush(c);
   if (rc != VCB_OK) return rc;
-  if (inside_empty && c->z_begin > 0)
-    return fail(c, VCB_ERR_UNSUPPORTED, "inside_empty needs the plane below the slab (single-GPU only)");
+  if (inside_empty && c->z_begin > 0 && !c->un_implied)
+    return fail(c, VCB_ERR_UNSUPPORTED,
+                "inside_empty on a z slab needs the uploaded grid to keep update_num < 1 <=> sdf == kVal "
+                "(update_num has no halo plane)");
   {
     Span span(c, 2);
     cudaError_t e = voxel_extract_count(grid_desc(c), inside_empty, &c->vox, c->stream,

@@ -168,7 +168,15 @@ __device__ __forceinline__ bool emit_predicate(const GridDesc& g, int inside_emp
   bool emit = false;
   if (x >= 1 && g.update_num[id - 1] >= 1) emit |= (__fmul_rn(s, g.sdf[id - 1]) < 0.0f) || tiny;
   if (y >= 1 && g.update_num[id - g.nx] >= 1) emit |= (__fmul_rn(s, g.sdf[id - g.nx]) < 0.0f) || tiny;
-  if (zl >= 1 && g.update_num[id - plane] >= 1) emit |= (__fmul_rn(s, g.sdf[id - plane]) < 0.0f) || tiny;
+  if (zl >= 1) {
+    if (g.update_num[id - plane] >= 1) emit |= (__fmul_rn(s, g.sdf[id - plane]) < 0.0f) || tiny;
+  } else if (g.z_begin > 0 && g.halo >= 1) {
+    // first plane of a z slab: the voxel below lives in the halo plane stored right under the slab
+    // (filled from the lower slab before this kernel runs); update_num has no halo, but a grid that
+    // was carved keeps update_num >= 1 <=> sdf != kVal (the caller checks that this holds)
+    const float below = (g.sdf - plane)[id];
+    if (below != kInvalidSdf) emit |= (__fmul_rn(s, below) < 0.0f) || tiny;
+  }
   return emit;
 }
 
@@ -300,7 +308,7 @@ cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, VoxelExtrac
   const SegGeom sg = seg_geom(g);
   st->n_voxels = -1;
   st->inside_empty = inside_empty;
-  if (inside_empty && g.z_begin > 0) return cudaErrorNotSupported;  // needs the plane below
+  if (inside_empty && g.z_begin > 0 && g.halo < 1) return cudaErrorNotSupported;  // needs the plane below
   const int64_t n_rows = (int64_t)g.ny * (g.z_end - g.z_begin);
   cudaError_t e;
   if ((e = st->bits.reserve((size_t)sg.n_segs * sizeof(uint32_t))) != cudaSuccess) return e;

@@ -1,21 +1,19 @@
-"""z-slab sharding of one voxel grid across GPUs.
+"""z-slab sharding of one voxel grid across GPUs: thin Python mirror of the
+vcb_sharded_* part of the C ABI (csrc/sharded.cu), where the whole engine lives - the split of the
+2D SDF work across the GPUs, the all-gather of the SDF images, the halo / count / vertex-id
+exchanges of marching cubes and the gather of the mesh.
 
-The reference is single-process; what is mirrored here is its result: the slabs together must
-produce exactly the grid, and exactly the marching-cubes mesh (same vertex numbering, same face
-order), that one carver over the whole grid produces.
+The reference is single-process; what is mirrored is its result: the slabs together produce exactly
+the grid, and exactly the marching-cubes mesh (same vertex numbering, same face order), that one
+carver over the whole grid produces.
 
-* fusion needs no exchange: every slab fuses every view into its own planes;
-* marching cubes needs (1) the two sdf planes below each slab (halo), (2) the per-slab vertex / face
-  counts to turn local numbers into global ones, (3) the ids of the vertices lying on the slab's
-  top plane, handed to the slab above.
-
-Two drivers share the same C-ABI phases:
-  `LocalSlabs`     all slabs in ONE process on one GPU (device-to-device copies) - used by the tests
-                   to prove the slab algorithm equals the unsharded result on a single GPU;
-  `ShardedCarver`  one process per GPU under torch.distributed (NCCL over NVLink; gloo for the
-                   CPU tests of the host logic): send/recv of halo planes and id planes,
-                   all_gather of the counts.
-torch is plumbing only (device buffers for NCCL, streams, the process group).
+  `LocalSlabs`     ONE process drives all slabs (vcb_sharded_create; peer copies between the
+                   devices).  With the same device listed N times the slabs are "virtual": the tests
+                   use that to prove the slab algorithm on a single GPU.
+  `ShardedCarver`  one process per GPU under torch.distributed (vcb_sharded_create_rank; NCCL inside
+                   the library).  torch only carries the NCCL unique id from rank 0 to the other
+                   ranks and the slab costs for re-balancing - no tensor of the data path is a torch
+                   tensor.
 """
 import ctypes as C
 
@@ -101,160 +99,245 @@ def assemble_ply(totals, parts):
     return head.raw + b"".join(p[0] for p in parts) + b"".join(p[1] for p in parts)
 
 
-class _DevArray:
-    """Exposes raw device memory of the carver to torch through __cuda_array_interface__."""
-
-    def __init__(self, ptr, shape, typestr):
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr,
-                                         "data": (int(ptr), False), "version": 2}
-
-
-def device_tensor(ptr, shape, typestr, device):
-    import torch
-    return torch.as_tensor(_DevArray(ptr, shape, typestr), device=device)
+def _options_struct(option):
+    from .carver import _fill_options
+    lib = capi.load_library()
+    o = capi.Options()
+    lib.vcb_options_default(C.byref(o))
+    _fill_options(o, option, 0, None)
+    return o
 
 
-class _Slab:
-    """One carver + torch views of its state / halo, and the phase calls."""
-
-    def __init__(self, option, z_range, device, stream=None):
-        import torch
-        self.car = VoxelCarver(option, device=device, z_range=z_range)
-        if not self.car.Init():
-            raise capi.VcbError(-1, self.car.last_error)
-        self.device = torch.device("cuda", device)
-        self.lib, self.h = self.car._lib, self.car._h
-        if stream is not None:
-            self.car.set_stream(stream.cuda_stream)
-        nx, ny, nz = self.car.dims
-        self.nx, self.ny = nx, ny
-        self.z0, self.z1 = self.car.z_range
-        sdf_ptr, _ = self.car.grid_device()
-        self.sdf = device_tensor(sdf_ptr, (self.z1 - self.z0, ny, nx), "<f4", self.device)
-        hp, hn = C.c_void_p(), C.c_int32()
-        capi.check(self.lib, self.h, self.lib.vcb_halo_device(self.h, C.byref(hp), C.byref(hn)))
-        self.halo_planes = hn.value
-        self.halo = (device_tensor(hp.value, (hn.value, ny, nx), "<f4", self.device)
-                     if hn.value else None)
-        self.ids_out = torch.empty((2, ny, nx), dtype=torch.int32, device=self.device)
-        self.ids_in = torch.empty((2, ny, nx), dtype=torch.int32, device=self.device)
-
-    def top_planes(self, n):
-        return self.sdf[self.sdf.shape[0] - n:]
-
-    def begin(self, iso, interp):
-        nv, nf = C.c_int64(), C.c_int64()
-        capi.check(self.lib, self.h, self.lib.vcb_extract_iso_begin(
-            self.h, float(iso), int(interp), C.byref(nv), C.byref(nf)))
-        return nv.value, nf.value
-
-    def vertices(self, offset):
-        capi.check(self.lib, self.h, self.lib.vcb_extract_iso_vertices(self.h, int(offset)))
-
-    def export_top(self):
-        capi.check(self.lib, self.h, self.lib.vcb_extract_iso_export_top(
-            self.h, C.c_void_p(self.ids_out.data_ptr())))
-        return self.ids_out
-
-    def import_bottom(self, ids):
-        capi.check(self.lib, self.h, self.lib.vcb_extract_iso_import_bottom(
-            self.h, C.c_void_p(ids.data_ptr())))
-
-    def faces(self):
-        capi.check(self.lib, self.h, self.lib.vcb_extract_iso_faces(self.h))
-
-    def mesh_host(self, nv, nf):
-        """This slab's mesh on the host.  The arrays are views of a pinned buffer the slab keeps and
-        reuses (pageable destinations make the copy several times slower): valid until the next
-        call, copy them to keep them."""
-        import torch
-        need = (nv + nf) * 12
-        if getattr(self, "_mesh_pin", None) is None or self._mesh_pin.numel() < need:
-            self._mesh_pin = torch.empty(max(need, 1) * 5 // 4, dtype=torch.uint8, pin_memory=True)
-        raw = self._mesh_pin.numpy()
-        v = raw[:nv * 12].view(np.float32).reshape(nv, 3)
-        f = raw[nv * 12:need].view(np.int32).reshape(nf, 3)
-        capi.check(self.lib, self.h, self.lib.vcb_extract_iso_fill(
-            self.h, v.ctypes.data_as(C.POINTER(C.c_float)), f.ctypes.data_as(C.POINTER(C.c_int32))))
-        return v, f
+def _bounds_array(ranges):
+    b = [ranges[0][0]] + [r[1] for r in ranges]
+    return (C.c_int32 * len(b))(*b)
 
 
-class LocalSlabs:
-    """N slabs of one grid in one process on one GPU: the multi-GPU algorithm with copies in place
-    of NCCL.  `extract_iso` returns the concatenated mesh, which must equal the unsharded one."""
+class _Engine:
+    """Owns a vcb_sharded handle; what LocalSlabs and ShardedCarver share."""
 
-    def __init__(self, option, n_slabs, device=0):
-        probe = VoxelCarver(option, device=device)
-        if not probe.Init():
-            raise capi.VcbError(-1, probe.last_error)
-        self.dims = probe.dims
-        probe.close()
-        self.slabs = [_Slab(option, zr, device) for zr in slab_ranges(self.dims[2], n_slabs)]
+    def __init__(self):
+        self._lib = capi.load_library()
+        self._h = None
+        self._pin = None
+
+    def _check(self, rc):
+        capi.check_sharded(self._lib, self._h, rc)
+
+    def _after_create(self, option):
+        self._option = option
+        w, nl = C.c_int32(), C.c_int32()
+        d = (C.c_int32 * 3)()
+        self._check(self._lib.vcb_sharded_info(self._h, C.byref(w), C.byref(nl), d))
+        self.world, self.n_local, self.dims = w.value, nl.value, (d[0], d[1], d[2])
+        self._refresh()
+
+    def _refresh(self):
+        b = (C.c_int32 * (self.world + 1))()
+        self._check(self._lib.vcb_sharded_bounds(self._h, b))
+        self.ranges = [(b[i], b[i + 1]) for i in range(self.world)]
+        self.slabs, self.local_ranks = [], []
+        for i in range(self.n_local):
+            h, r = C.c_void_p(), C.c_int32()
+            self._check(self._lib.vcb_sharded_local(self._h, i, C.byref(h), C.byref(r)))
+            self.slabs.append(VoxelCarver.borrowed(h.value, self._option))
+            self.local_ranks.append(r.value)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.slabs = []
+            self._lib.vcb_sharded_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    # ---- carving ----------------------------------------------------------------------------------
+    def reset(self):
+        self._check(self._lib.vcb_sharded_reset(self._h))
+
+    def make_views(self, cameras, width, height):
+        return [make_view(c, width, height) for c in cameras]
+
+    def carve_views(self, views, masks, device=False):
+        """masks: numpy uint8 arrays (HOST) or integers (DEVICE pointers readable from the owning
+        GPU); views fused in call order, 64 per launch."""
+        n = len(views)
+        if n == 0:
+            return
+        arr = (capi.View * n)(*views)
+        ptrs = (C.c_void_p * n)()
+        for i, m in enumerate(masks):
+            ptrs[i] = m if isinstance(m, int) else m.ctypes.data
+        fn = (self._lib.vcb_sharded_carve_masks_device if device
+              else self._lib.vcb_sharded_carve_masks)
+        self._check(fn(self._h, n, arr, ptrs, None))
 
     def carve_batch(self, cameras, images):
-        for s in self.slabs:
-            assert s.car.carve_batch(cameras, images)
+        imgs = [np.ascontiguousarray(i, np.uint8) for i in images]
+        views = [make_view(c, m.shape[1], m.shape[0]) for c, m in zip(cameras, imgs)]
+        self.carve_views(views, imgs)
+        return True
+
+    def flush(self):
+        self._check(self._lib.vcb_sharded_flush(self._h))
+
+    def synchronize(self):
+        self._check(self._lib.vcb_sharded_synchronize(self._h))
+
+    # ---- extraction -------------------------------------------------------------------------------
+    def extract_iso_counts(self, iso=0.0, interp=True):
+        """Runs marching cubes over the whole grid, every slab's part of the mesh staying on its
+        GPU; returns the GLOBAL (vertices, faces) counts (the same on every rank)."""
+        nv, nf = C.c_int64(), C.c_int64()
+        self._check(self._lib.vcb_sharded_extract_iso_count(self._h, float(iso), int(interp),
+                                                            C.byref(nv), C.byref(nf)))
+        self._totals = (nv.value, nf.value)
+        return self._totals
+
+    def _pinned(self, nbytes):
+        import torch
+        if self._pin is None or self._pin.numel() < nbytes:
+            self._pin = torch.empty(max(nbytes, 1) * 5 // 4, dtype=torch.uint8, pin_memory=True)
+        return self._pin.numpy()
+
+    def mesh_host(self, receive=True):
+        """The WHOLE mesh of the last extract_iso_counts on the host: (vertices [V,3] float32, faces
+        [F,3] int32), views of a pinned buffer that is reused by the next call.  With one process
+        per GPU only rank 0 receives it (receive=False on the others, which just send their
+        part and get None)."""
+        nv, nf = self._totals
+        if not receive:
+            self._check(self._lib.vcb_sharded_extract_iso_fill(self._h, None, None))
+            return None
+        raw = self._pinned((nv + nf) * 12)
+        v = raw[:nv * 12].view(np.float32).reshape(nv, 3)
+        f = raw[nv * 12:(nv + nf) * 12].view(np.int32).reshape(nf, 3)
+        self._check(self._lib.vcb_sharded_extract_iso_fill(
+            self._h, v.ctypes.data_as(C.POINTER(C.c_float)), f.ctypes.data_as(C.POINTER(C.c_int32))))
+        return v, f
+
+    def local_mesh_counts(self, i=0):
+        a = [C.c_int64() for _ in range(4)]
+        self._check(self._lib.vcb_sharded_local_mesh(self._h, i, *[C.byref(x) for x in a]))
+        return tuple(x.value for x in a)  # vertices, faces, vertex offset, face offset
+
+    def extract_voxel_count(self, inside_empty=False):
+        n = C.c_int64()
+        self._check(self._lib.vcb_sharded_extract_voxel_count(self._h, int(inside_empty), C.byref(n)))
+        return n.value
+
+    def main_stream(self, i=0):
+        """cudaStream_t (as an integer) that orders slab i's reset, fusion and extraction."""
+        p = C.c_void_p()
+        self._check(self._lib.vcb_sharded_stream(self._h, i, C.byref(p)))
+        return p.value or 0
+
+    def stage_times(self, i=0):
+        ms = (C.c_float * 4)()
+        n = (C.c_int64 * 4)()
+        self._check(self._lib.vcb_sharded_stage_times(self._h, i, ms, n))
+        names = ("sdf2d", "fusion", "extract_voxel", "marching_cubes")
+        return {k: (ms[j], n[j]) for j, k in enumerate(names)}
+
+
+class LocalSlabs(_Engine):
+    """N slabs of one grid driven by ONE process (vcb_sharded_create).  `devices` lists the CUDA
+    device of every slab; the default puts all `n_slabs` on one GPU ("virtual slabs"), which runs
+    the multi-GPU algorithm - 2D SDF split, gathers, halo and id exchanges - on a single device."""
+
+    def __init__(self, option, n_slabs, device=0, devices=None, ranges=None):
+        super().__init__()
+        devices = list(devices) if devices is not None else [device] * n_slabs
+        o = _options_struct(option)
+        h = C.c_void_p()
+        dev = (C.c_int32 * len(devices))(*devices)
+        rc = self._lib.vcb_sharded_create(C.byref(o), dev, len(devices),
+                                          _bounds_array(ranges) if ranges else None, C.byref(h))
+        if rc != 0:
+            raise capi.VcbError(rc, self._lib.vcb_last_error(None).decode())
+        self._h = h
+        self._after_create(option)
 
     def download_grid(self):
-        parts = [s.car.download_grid() for s in self.slabs]
+        self.flush()
+        parts = [s.download_grid() for s in self.slabs]
         return np.concatenate([p[0] for p in parts]), np.concatenate([p[1] for p in parts])
 
     def extract_iso(self, iso=0.0, interp=True):
-        import torch
-        for lo, hi in zip(self.slabs[:-1], self.slabs[1:]):
-            lo.car.flush()
-            hi.car.flush()
-            torch.cuda.synchronize()
-            hi.halo.copy_(lo.top_planes(hi.halo_planes))
-        torch.cuda.synchronize()
-        counts = [s.begin(iso, interp) for s in self.slabs]
-        off, total = exclusive_offsets(counts)
-        for s, o in zip(self.slabs, off):
-            s.vertices(o[0])
-        torch.cuda.synchronize()
-        for lo, hi in zip(self.slabs[:-1], self.slabs[1:]):
-            ids = lo.export_top()
-            torch.cuda.synchronize()
-            hi.import_bottom(ids)
-        for s in self.slabs:
-            s.faces()
-        parts = [s.mesh_host(*c) for s, c in zip(self.slabs, counts)]
-        self._totals = (int(total[0]), int(total[1]))
-        return np.concatenate([p[0] for p in parts]), np.concatenate([p[1] for p in parts])
+        self.extract_iso_counts(iso, interp)
+        v, f = self.mesh_host()
+        return v.copy(), f.copy()
 
     def ply_text(self):
         """ASCII PLY of the mesh of the last extract_iso, assembled from the slabs' text blocks:
         header for the global counts, every slab's vertex lines, then every slab's face lines."""
-        return assemble_ply(self._totals, [s.car.ply_text(header=False, split=True)
-                                           for s in self.slabs])
+        return assemble_ply(self._totals, [s.ply_text(header=False, split=True) for s in self.slabs])
 
     def occupancy(self, inside_empty=False):
-        parts = [s.car.occupancy(inside_empty) for s in self.slabs]
-        return np.concatenate([p[0] for p in parts]), sum(p[1] for p in parts)
+        total = self.extract_voxel_count(inside_empty)
+        flags = []
+        for s in self.slabs:
+            buf = np.empty(s.slab_voxels, np.uint8)
+            s._check(s._lib.vcb_extract_voxel_occupancy(
+                s._h, buf.ctypes.data_as(C.POINTER(C.c_uint8))))
+            flags.append(buf)
+        return np.concatenate(flags), total
+
+    def extract_voxel(self, inside_empty=False):
+        n = self.extract_voxel_count(inside_empty)
+        v = np.empty((n * 24, 3), np.float32)
+        f = np.empty((n * 12, 3), np.int32)
+        if n:
+            self._check(self._lib.vcb_sharded_extract_voxel_fill(
+                self._h, v.ctypes.data_as(C.POINTER(C.c_float)),
+                f.ctypes.data_as(C.POINTER(C.c_int32))))
+        return v, f
 
 
-class ShardedCarver:
-    """This rank's slab of the grid under torch.distributed (world == 1: the whole grid)."""
+def broadcast_unique_id(rank, world, group=None, device=None):
+    """The 128-byte NCCL id of vcb_sharded_unique_id, made on rank 0 and broadcast through
+    torch.distributed (on `device` for an NCCL process group, on the CPU for gloo)."""
+    import torch
+    import torch.distributed as dist
+    lib = capi.load_library()
+    buf = (C.c_uint8 * capi.UNIQUE_ID_BYTES)()
+    if rank == 0:
+        capi.check(lib, None, lib.vcb_sharded_unique_id(buf))
+    t = torch.tensor(list(buf), dtype=torch.uint8, device=device if device is not None else "cpu")
+    if world > 1:
+        dist.broadcast(t, src=0, group=group)
+    return bytes(t.cpu().tolist())
 
-    def __init__(self, option, rank, world, device, stream=None, group=None):
+
+class ShardedCarver(_Engine):
+    """This rank's slab of the grid, one process per GPU (world == 1: the whole grid)."""
+
+    def __init__(self, option, rank, world, device, stream=None, group=None, ranges=None):
+        super().__init__()
         import torch
-        self.rank, self.world, self.group = rank, world, group
-        self.torch = torch
-        # number of z planes as VoxelGrid::Init computes it (float32, voxel_carver.cc:294-296)
-        nz = int((np.float32(option.bb_max[2]) - np.float32(option.bb_min[2])) /
-                 np.float32(option.resolution))
-        self.option, self.device_index = option, device
-        self.ranges = slab_ranges(nz, world) if world > 1 else [(0, nz)]
-        self.stream = stream if stream is not None else torch.cuda.current_stream()
-        self._build()
+        self.rank, self.group, self.torch = rank, group, torch
+        self.device_index = device
+        o = _options_struct(option)
+        uid = None
+        if world > 1:
+            on = torch.device("cuda", device) if torch.distributed.get_backend(group) == "nccl" else None
+            uid = broadcast_unique_id(rank, world, group, on)
+        h = C.c_void_p()
+        rc = self._lib.vcb_sharded_create_rank(C.byref(o), device, rank, world, uid,
+                                               _bounds_array(ranges) if ranges else None, C.byref(h))
+        if rc != 0:
+            raise capi.VcbError(rc, self._lib.vcb_last_error(None).decode())
+        self._h = h
+        self._after_create(option)
 
-    def _build(self):
-        self.z_range = self.ranges[self.rank] if self.world > 1 else None
-        self.slab = _Slab(self.option, self.z_range, self.device_index, self.stream)
-        self.car = self.slab.car
-        self.dims = self.car.dims
-        self.slab_voxels = self.car.slab_voxels
-        self._counts = None
+    @property
+    def car(self):
+        return self.slabs[0]
+
+    @property
+    def slab_voxels(self):
+        return self.slabs[0].slab_voxels
 
     def rebalance(self, my_cost):
         """Re-partitions the grid so that every slab carries about the same measured cost (call
@@ -263,122 +346,35 @@ class ShardedCarver:
         if self.world == 1:
             return self.ranges
         torch = self.torch
-        mine = torch.tensor([float(my_cost)], dtype=torch.float64, device=self.slab.device)
+        on = torch.device("cuda", self.device_index) if torch.distributed.get_backend(self.group) == "nccl" else "cpu"
+        mine = torch.tensor([float(my_cost)], dtype=torch.float64, device=on)
         allc = [torch.empty_like(mine) for _ in range(self.world)]
         torch.distributed.all_gather(allc, mine, group=self.group)
         cost = [float(t.item()) for t in allc]
         new = rebalanced_ranges(self.ranges, cost, quantum=FUSION_TILE_PLANES)
         if new != self.ranges:
-            self.ranges = new
-            self.car.synchronize()
-            self.slab.car.close()
-            self.slab = None
-            self._build()
+            self.slabs = []
+            self._check(self._lib.vcb_sharded_repartition(self._h, _bounds_array(new)))
+            self._refresh()
         return self.ranges
 
-    # ---- carving: no exchange -----------------------------------------------------------------
-    def reset(self):
-        self.car.reset()
-
-    def make_views(self, cameras, width, height):
-        return [make_view(c, width, height) for c in cameras]
-
     def carve_device_masks(self, views, dev_masks):
-        """dev_masks: torch uint8 [V, H, W] on this rank's GPU."""
+        """dev_masks: torch uint8 [V, H, W] on this rank's GPU (every rank holds all masks; only a
+        view's owner reads its mask)."""
         stride = dev_masks.stride(0)
         base = dev_masks.data_ptr()
-        self.car.carve_device(views, [base + i * stride for i in range(dev_masks.shape[0])],
-                              masks=True)
+        self.carve_views(views, [base + i * stride for i in range(dev_masks.shape[0])], device=True)
 
-    def carve_host_masks(self, cameras, host_masks, chunk=64):
-        """Masks in HOST memory (pinned for asynchronous copies). One GPU: straight through the host
-        entry point. Several GPUs: every rank uploads only its 1/world share over its own PCIe link
-        and the shares are all-gathered over NVLink (NCCL), so no rank moves the whole set from the
-        host; then each rank fuses every view into its slab.  The upload + all-gather runs on a side
-        stream in chunks of `chunk` views (one fusion launch), so the masks of the next launch travel
-        while the current one is being fused."""
-        if self.world == 1:
-            assert self.car.carve_batch(cameras, host_masks)
-            return
-        torch = self.torch
-        n = len(host_masks)
+    def carve_host_masks(self, cameras, host_masks):
+        """Masks in HOST memory (pinned for asynchronous copies): each rank uploads only the masks of
+        the views it owns, over its own PCIe link."""
         h, w = host_masks[0].shape
-        plan, total = [], 0  # (first view, views, views per rank, offset in the device buffer)
-        for first in range(0, n, chunk):
-            cnt = min(chunk, n - first)
-            per = (cnt + self.world - 1) // self.world
-            plan.append((first, cnt, per, total))
-            total += per * self.world
-        buf = getattr(self, "_mask_buf", None)
-        if buf is None or tuple(buf.shape) != (total, h, w):
-            buf = self._mask_buf = torch.empty((total, h, w), dtype=torch.uint8,
-                                               device=self.slab.device)
-        side = getattr(self, "_side_stream", None)
-        if side is None:
-            side = self._side_stream = torch.cuda.Stream(device=self.slab.device)
-        side.wait_stream(self.stream)  # kernels of the previous pass may still read the buffer
-        events = []
-        with torch.cuda.stream(side):
-            for first, cnt, per, off in plan:
-                lo, hi = min(cnt, self.rank * per), min(cnt, (self.rank + 1) * per)
-                for i in range(lo, hi):
-                    buf[off + i].copy_(torch.from_numpy(host_masks[first + i]), non_blocking=True)
-                mine = buf[off + self.rank * per:off + (self.rank + 1) * per]
-                torch.distributed.all_gather_into_tensor(
-                    buf[off:off + per * self.world].view(self.world, -1), mine.view(-1),
-                    group=self.group)
-                ev = torch.cuda.Event()
-                ev.record(side)
-                events.append(ev)
-        views = self.make_views(cameras, w, h)
-        for (first, cnt, per, off), ev in zip(plan, events):
-            self.stream.wait_event(ev)
-            self.carve_device_masks(views[first:first + cnt], buf[off:off + cnt])
-
-    # ---- marching cubes ---------------------------------------------------------------------------
-    def _sendrecv(self, send, recv):
-        """send -> rank + 1, recv <- rank - 1 (either may be None), ordered on the carver's stream."""
-        dist = self.torch.distributed
-        ops = []
-        if send is not None and self.rank + 1 < self.world:
-            ops.append(dist.P2POp(dist.isend, send, self.rank + 1, self.group))
-        if recv is not None and self.rank > 0:
-            ops.append(dist.P2POp(dist.irecv, recv, self.rank - 1, self.group))
-        if ops:
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
-
-    def extract_iso_counts(self, iso=0.0, interp=True):
-        """Runs the extraction, leaving this rank's part of the mesh on its GPU; returns the GLOBAL
-        (vertices, faces) counts."""
-        torch = self.torch
-        s = self.slab
-        if self.world == 1:
-            nv, nf = s.begin(iso, interp)
-            s.vertices(0)
-            s.faces()
-            self._counts = (nv, nf)
-            self._offsets = (0, 0)
-            return nv, nf
-        with torch.cuda.stream(self.stream):
-            self.car.flush()
-            # the slab above keeps min(2, z_begin) halo planes; every slab has >= 2 planes
-            self._sendrecv(s.top_planes(2).contiguous(), s.halo)
-            nv, nf = s.begin(iso, interp)
-            off, total = gather_offsets(nv, nf, self.world, self.group, s.device)
-            s.vertices(off[self.rank][0])
-            self._sendrecv(s.export_top(), s.ids_in)
-            if self.rank > 0:
-                s.import_bottom(s.ids_in)
-            s.faces()
-        self._counts = (nv, nf)
-        self._offsets = tuple(int(x) for x in off[self.rank])
-        return int(total[0]), int(total[1])
+        self.carve_views(self.make_views(cameras, w, h), host_masks)
 
     def extract_iso_host(self, iso=0.0, interp=True):
-        """Extraction + copy of THIS rank's part of the mesh to the host (vertex ids are global)."""
+        """Extraction + the WHOLE mesh on rank 0's host (None on the other ranks)."""
         self.extract_iso_counts(iso, interp)
-        return self.slab.mesh_host(*self._counts)
+        return self.mesh_host(receive=self.rank == 0)
 
     def ply_parts(self):
         """(vertex_text, face_text) of THIS rank's part of the last extracted mesh (global ids)."""
@@ -393,6 +389,3 @@ class ShardedCarver:
         parts = [None] * self.world if self.rank == 0 else None
         self.torch.distributed.gather_object(mine, parts, dst=0, group=self.group)
         return assemble_ply(totals, parts) if self.rank == 0 else None
-
-    def stage_times(self):
-        return self.car.stage_times()

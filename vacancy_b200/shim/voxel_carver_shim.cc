@@ -12,31 +12,90 @@
 //
 // The reference class has no member that could hold a device handle (voxel_carver.h:95-97), and the
 // header must not change, so carvers are tracked in a side table keyed by `this`; the AoS
-// `voxel_grid_` member is simply never allocated (the grid lives on the device as SoA).
+// `voxel_grid_` member is simply never allocated (the grid lives on the device as SoA).  Because
+// the key is the object's address, a VoxelCarver must stay where it was when Init() ran: a copy or
+// a moved-to object has no device grid (Carve returns false on it, as before Init), and the
+// original keeps its handle until it is destroyed.
+//
+// Placement comes from the environment, so that host code needs no change to use more GPUs:
+//   VACANCY_B200_DEVICE=<n>        the one GPU to run on (default 0);
+//   VACANCY_B200_DEVICES=0,1,2,3   carve ONE grid on several GPUs (z slabs, vcb_sharded_*): same
+//                                  calls, same results, the mesh arrives whole.
 #include "vacancy/voxel_carver.h"
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <mutex>
 #include <unordered_map>
+#include <vector>
 
 #include "vacancy_b200.h"
 #include "vacancy_b200_batch.h"
 
 namespace {
 
-std::mutex g_mutex;
-std::unordered_map<const vacancy::VoxelCarver*, vcb_carver*> g_carvers;
+// One grid: either a single carver or a z-slab engine over several GPUs; the calls below dispatch.
+struct Handle {
+  vcb_carver* one = nullptr;
+  vcb_sharded* many = nullptr;
+  const char* error() const { return many ? vcb_sharded_last_error(many) : vcb_last_error(one); }
+  int carve_masks(int32_t n, const vcb_view* v, const uint8_t* const* m, float* const* out) const {
+    return many ? vcb_sharded_carve_masks(many, n, v, m, out) : vcb_carve_masks(one, n, v, m, out);
+  }
+  int carve_sdfs(int32_t n, const vcb_view* v, const float* const* img) const {
+    return many ? vcb_sharded_carve_sdfs(many, n, v, img) : vcb_carve_sdfs(one, n, v, img);
+  }
+  int iso_count(double iso, int32_t interp, int64_t* nv, int64_t* nf) const {
+    return many ? vcb_sharded_extract_iso_count(many, iso, interp, nv, nf)
+                : vcb_extract_iso_count(one, iso, interp, nv, nf);
+  }
+  int iso_fill(float* v, int32_t* f) const {
+    return many ? vcb_sharded_extract_iso_fill(many, v, f) : vcb_extract_iso_fill(one, v, f);
+  }
+  int voxel_count(int32_t inside_empty, int64_t* n) const {
+    return many ? vcb_sharded_extract_voxel_count(many, inside_empty, n)
+                : vcb_extract_voxel_count(one, inside_empty, n);
+  }
+  int voxel_fill(float* v, int32_t* f) const {
+    return many ? vcb_sharded_extract_voxel_fill(many, v, f) : vcb_extract_voxel_fill(one, v, f);
+  }
+  // the carvers that hold the parts of the last extracted mesh, in slab order
+  std::vector<vcb_carver*> parts() const {
+    std::vector<vcb_carver*> out;
+    if (!many) {
+      out.push_back(one);
+      return out;
+    }
+    int32_t n_local = 0;
+    vcb_sharded_info(many, nullptr, &n_local, nullptr);
+    for (int32_t i = 0; i < n_local; i++) {
+      vcb_carver* c = nullptr;
+      vcb_sharded_local(many, i, &c, nullptr);
+      out.push_back(c);
+    }
+    return out;
+  }
+  void destroy() {
+    if (one) vcb_destroy(one);
+    if (many) vcb_sharded_destroy(many);
+    one = nullptr;
+    many = nullptr;
+  }
+};
 
-vcb_carver* find_carver(const vacancy::VoxelCarver* self) {
+std::mutex g_mutex;
+std::unordered_map<const vacancy::VoxelCarver*, Handle> g_carvers;
+
+const Handle* find_carver(const vacancy::VoxelCarver* self) {
   std::lock_guard<std::mutex> lock(g_mutex);
   auto it = g_carvers.find(self);
-  return it == g_carvers.end() ? nullptr : it->second;
+  return it == g_carvers.end() ? nullptr : &it->second;  // node addresses are stable
 }
 
 void drop_carver(const vacancy::VoxelCarver* self) {
-  vcb_carver* h = nullptr;
+  Handle h;
   {
     std::lock_guard<std::mutex> lock(g_mutex);
     auto it = g_carvers.find(self);
@@ -45,12 +104,28 @@ void drop_carver(const vacancy::VoxelCarver* self) {
       g_carvers.erase(it);
     }
   }
-  if (h != nullptr) vcb_destroy(h);
+  h.destroy();
 }
 
 int device_ordinal() {
   const char* e = std::getenv("VACANCY_B200_DEVICE");
   return e != nullptr ? std::atoi(e) : 0;
+}
+
+// VACANCY_B200_DEVICES=0,1,... -> device list (empty: single-GPU mode)
+std::vector<int32_t> device_list() {
+  std::vector<int32_t> out;
+  const char* e = std::getenv("VACANCY_B200_DEVICES");
+  if (e == nullptr) return out;
+  for (const char* p = e; *p != 0;) {
+    char* end = nullptr;
+    const long v = std::strtol(p, &end, 10);
+    if (end == p) break;
+    out.push_back(static_cast<int32_t>(v));
+    p = (*end == ',') ? end + 1 : end;
+    if (*end != ',' && *end != 0) break;
+  }
+  return out;
 }
 
 // Camera -> vcb_view. The fusion kernel restates exactly two projection models (camera.cc:131-137
@@ -83,9 +158,9 @@ bool make_view(const vacancy::Camera& camera, int width, int height,
   return true;
 }
 
-bool report(const vcb_carver* h, int rc, const char* what) {
+bool report(const Handle* h, int rc, const char* what) {
   if (rc == VCB_OK) return true;
-  vacancy::LOGE("%s: %s\n", what, vcb_last_error(h));
+  vacancy::LOGE("%s: %s\n", what, h != nullptr ? h->error() : vcb_last_error(nullptr));
   return false;
 }
 
@@ -217,8 +292,18 @@ bool VoxelCarver::Init() {  // voxel_carver.cc:375-392; calling it again re-crea
   o.use_truncation = u.use_truncation ? 1 : 0;
   o.truncation_band = u.truncation_band;
   o.device = device_ordinal();
-  vcb_carver* h = nullptr;
-  if (!report(nullptr, vcb_create(&o, &h), "VoxelCarver::Init")) return false;
+  Handle h;
+  const std::vector<int32_t> devices = device_list();
+  if (devices.size() > 1) {
+    if (!report(nullptr,
+                vcb_sharded_create(&o, devices.data(), static_cast<int32_t>(devices.size()), nullptr,
+                                   &h.many),
+                "VoxelCarver::Init"))
+      return false;
+  } else {
+    if (devices.size() == 1) o.device = devices[0];
+    if (!report(nullptr, vcb_create(&o, &h.one), "VoxelCarver::Init")) return false;
+  }
   std::lock_guard<std::mutex> lock(g_mutex);
   g_carvers[this] = h;
   return true;
@@ -227,7 +312,7 @@ bool VoxelCarver::Init() {  // voxel_carver.cc:375-392; calling it again re-crea
 bool VoxelCarver::Carve(const Camera& camera, const Image1b& silhouette,
                         const Eigen::Vector2i& roi_min, const Eigen::Vector2i& roi_max,
                         Image1f* sdf) {
-  vcb_carver* h = find_carver(this);
+  const Handle* h = find_carver(this);
   if (h == nullptr) {  // the reference dereferences a null grid here (voxel_carver.cc:397)
     LOGE("VoxelCarver::Carve voxel grid has not been initialized\n");
     return false;
@@ -242,13 +327,13 @@ bool VoxelCarver::Carve(const Camera& camera, const Image1b& silhouette,
     sdf->Init(silhouette.width(), silhouette.height(), 0.0f);
     out = sdf->data_ptr()->data();
   }
-  return report(h, vcb_carve_masks(h, 1, &view, &mask, sdf != nullptr ? &out : nullptr),
+  return report(h, h->carve_masks(1, &view, &mask, sdf != nullptr ? &out : nullptr),
                 "VoxelCarver::Carve");
 }
 
 bool VoxelCarver::Carve(const Camera& camera, const Eigen::Vector2i& roi_min,
                         const Eigen::Vector2i& roi_max, const Image1f& sdf) {
-  vcb_carver* h = find_carver(this);
+  const Handle* h = find_carver(this);
   if (h == nullptr) {
     LOGE("VoxelCarver::Carve voxel grid has not been initialized\n");
     return false;
@@ -256,7 +341,7 @@ bool VoxelCarver::Carve(const Camera& camera, const Eigen::Vector2i& roi_min,
   vcb_view view;
   if (!make_view(camera, sdf.width(), sdf.height(), roi_min, roi_max, &view)) return false;
   const float* img = sdf.data().data();
-  return report(h, vcb_carve_sdfs(h, 1, &view, &img), "VoxelCarver::Carve");
+  return report(h, h->carve_sdfs(1, &view, &img), "VoxelCarver::Carve");
 }
 
 bool VoxelCarver::Carve(const Camera& camera, const Image1b& silhouette) {
@@ -298,15 +383,15 @@ void fill_mesh(Mesh* mesh, const std::vector<float>& v, const std::vector<int32_
 
 void VoxelCarver::ExtractVoxel(Mesh* mesh, bool inside_empty) {  // voxel_carver.cc:530-538
   mesh->Clear();
-  vcb_carver* h = find_carver(this);
+  const Handle* h = find_carver(this);
   if (h == nullptr) return;
   int64_t n = 0;
-  if (!report(h, vcb_extract_voxel_count(h, inside_empty ? 1 : 0, &n), "VoxelCarver::ExtractVoxel")) {
+  if (!report(h, h->voxel_count(inside_empty ? 1 : 0, &n), "VoxelCarver::ExtractVoxel")) {
     return;
   }
   std::vector<float> v(static_cast<size_t>(n) * 72);
   std::vector<int32_t> f(static_cast<size_t>(n) * 36);
-  if (n > 0 && !report(h, vcb_extract_voxel_fill(h, v.data(), f.data()), "VoxelCarver::ExtractVoxel")) {
+  if (n > 0 && !report(h, h->voxel_fill(v.data(), f.data()), "VoxelCarver::ExtractVoxel")) {
     return;
   }
   fill_mesh(mesh, v, f);
@@ -314,16 +399,16 @@ void VoxelCarver::ExtractVoxel(Mesh* mesh, bool inside_empty) {  // voxel_carver
 
 void VoxelCarver::ExtractIsoSurface(Mesh* mesh, double iso_level, bool linear_interp) {
   mesh->Clear();  // marching_cubes.cc:68
-  vcb_carver* h = find_carver(this);
+  const Handle* h = find_carver(this);
   if (h == nullptr) return;
   int64_t nv = 0, nf = 0;
-  if (!report(h, vcb_extract_iso_count(h, iso_level, linear_interp ? 1 : 0, &nv, &nf),
+  if (!report(h, h->iso_count(iso_level, linear_interp ? 1 : 0, &nv, &nf),
               "VoxelCarver::ExtractIsoSurface")) {
     return;
   }
   std::vector<float> v(static_cast<size_t>(nv) * 3);
   std::vector<int32_t> f(static_cast<size_t>(nf) * 3);
-  if (!report(h, vcb_extract_iso_fill(h, v.data(), f.data()), "VoxelCarver::ExtractIsoSurface")) {
+  if (!report(h, h->iso_fill(v.data(), f.data()), "VoxelCarver::ExtractIsoSurface")) {
     return;
   }
   fill_mesh(mesh, v, f);
@@ -339,7 +424,7 @@ bool CarveBatch(vacancy::VoxelCarver* carver, const std::vector<const vacancy::C
     vacancy::LOGE("CarveBatch: need a carver and as many cameras as silhouettes\n");
     return false;
   }
-  vcb_carver* h = find_carver(carver);
+  const Handle* h = find_carver(carver);
   if (h == nullptr) {
     vacancy::LOGE("VoxelCarver::Carve voxel grid has not been initialized\n");
     return false;
@@ -354,8 +439,8 @@ bool CarveBatch(vacancy::VoxelCarver* carver, const std::vector<const vacancy::C
     }
     masks[i] = m.data().data();
   }
-  return report(h, vcb_carve_masks(h, static_cast<int32_t>(views.size()), views.data(),
-                                   masks.data(), nullptr),
+  return report(h, h->carve_masks(static_cast<int32_t>(views.size()), views.data(), masks.data(),
+                                  nullptr),
                 "CarveBatch");
 }
 
@@ -373,23 +458,39 @@ bool write_file(const std::string& path, const std::vector<char>& text) {
 
 bool ExtractIsoSurfaceToPly(vacancy::VoxelCarver* carver, const std::string& ply_path,
                             double iso_level, bool linear_interp) {
-  vcb_carver* h = carver ? find_carver(carver) : nullptr;
+  const Handle* h = carver ? find_carver(carver) : nullptr;
   if (h == nullptr) {
     vacancy::LOGE("ExtractIsoSurfaceToPly: voxel grid has not been initialized\n");
     return false;
   }
   int64_t nv = 0, nf = 0;
-  if (!report(h, vcb_extract_iso_count(h, iso_level, linear_interp ? 1 : 0, &nv, &nf),
-              "ExtractIsoSurfaceToPly"))
+  if (!report(h, h->iso_count(iso_level, linear_interp ? 1 : 0, &nv, &nf), "ExtractIsoSurfaceToPly"))
     return false;
-  size_t hb = 0, vb = 0, fb = 0;
+  // the file is the header for the global counts, every slab's vertex lines in slab order, then
+  // every slab's face lines (vertex ids are already global)
+  const std::vector<vcb_carver*> parts = h->parts();
+  std::vector<size_t> vb(parts.size()), fb(parts.size());
+  size_t hb = 0, total_v = 0, total_f = 0;
   vcb_ply_header(nv, nf, nullptr, 0, &hb);
-  if (!report(h, vcb_ply_body_size(h, &vb, &fb), "ExtractIsoSurfaceToPly")) return false;
-  std::vector<char> text(hb + vb + fb);
+  for (size_t i = 0; i < parts.size(); i++) {
+    if (vcb_ply_body_size(parts[i], &vb[i], &fb[i]) != VCB_OK) {
+      vacancy::LOGE("ExtractIsoSurfaceToPly: %s\n", vcb_last_error(parts[i]));
+      return false;
+    }
+    total_v += vb[i];
+    total_f += fb[i];
+  }
+  std::vector<char> text(hb + total_v + total_f);
   vcb_ply_header(nv, nf, text.data(), text.size(), nullptr);
-  if (!report(h, vcb_ply_body_fill(h, text.data() + hb, text.data() + hb + vb),
-              "ExtractIsoSurfaceToPly"))
-    return false;
+  size_t ov = hb, of = hb + total_v;
+  for (size_t i = 0; i < parts.size(); i++) {
+    if (vcb_ply_body_fill(parts[i], text.data() + ov, text.data() + of) != VCB_OK) {
+      vacancy::LOGE("ExtractIsoSurfaceToPly: %s\n", vcb_last_error(parts[i]));
+      return false;
+    }
+    ov += vb[i];
+    of += fb[i];
+  }
   return write_file(ply_path, text);
 }
 
