@@ -275,12 +275,14 @@ def run_ours(args, cfg):
     else:
         ranges = car.ranges
     car.stage_times()  # clear the per-stage counters
+    car.car.fusion_class_counts()  # ... and the tile-class counters
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms_total, counts = timed(step_resident, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     stages = car.stage_times()
+    classes = car.car.fusion_class_counts()  # (tile, view) pairs of this rank's launches, by class
     ms_step = ms_total / args.steps
     per_rank = None
     if world > 1:  # how evenly the slabs split the work (rank order = slab order, bottom to top)
@@ -341,6 +343,48 @@ def run_ours(args, cfg):
             issue = {k: t[k] for k in ("thread_instructions_per_voxel_view", "issue_active",
                                        "fma_pipe_active", "source") if k in t}
 
+    # ---- what binds fuse_kernel (batched fusion is bound by FP32 issue, not HBM) ----
+    # The classification kernel counts the (tile, view) pairs per class; a pair is 2048 voxel-views.
+    # Work is counted over EXECUTED pairs only: the sampling classes at the reference's operation count
+    # per voxel-view (54 weighted / 48 kMax: w2c 18, z test 1, project 6, ROI test 4, bilinear 17,
+    # truncation test 1, update 7 / 1), the load-free "all ones" class without the four texel products,
+    # the ROI test and the truncation test (44 / 38); skipped pairs count nothing.  Peak = the packed
+    # FP32 issue rate measured on a B200 (FFMA2 / FADD2 microbenchmark, 36.95 T lane-ops/s at 1965 MHz,
+    # profiles/r01_f32x2_issue_microbench.txt), scaled to the SM clock sampled during this run.
+    vpt = classes["voxels_per_tile"]
+    ops_s = 54.0 if cfg["weighted"] else 48.0
+    ops_1 = ops_s - 10.0
+    pairs_s = classes["general"] + classes["inside"]
+    pairs_1 = classes["all_ones"]
+    pairs_skip = classes["all_kval"] + classes["outside"]
+    pairs_all = max(1, pairs_s + pairs_1 + pairs_skip)
+    executed_vv = float(pairs_s + pairs_1) * vpt / args.steps  # this rank, per step
+    lane_ops = (pairs_s * ops_s + pairs_1 * ops_1) * vpt / args.steps
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    fp32_peak = 36.95 * sm_mhz / 1965.0
+    fp32_achieved = lane_ops / (fus_ms / args.steps * 1e-3) / 1e12
+    hbm = {"kernel": "fuse_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+           "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
+           "traffic_source": "ncu --set full capture of a 64-view launch, scaled to the average "
+                             "views per launch (profiles/fuse_kernel_traffic.json)" if traffic else None,
+           "bytes_per_launch": bytes_per_launch, "ms_per_launch": fus_ms_per_launch,
+           "note": "algorithmic bytes (16 B per voxel + 4 B per SDF pixel per launch): HBM does not "
+                   "bind a 64-view launch"}
+    roofline = {"kernel": "fuse_kernel", "bound": "fp32_issue", "achieved": fp32_achieved,
+                "peak": fp32_peak, "unit": "T lane-ops/s", "frac": fp32_achieved / fp32_peak,
+                "traffic": traffic,
+                "peak_source": "measured packed-FP32 issue rate of a B200 (profiles/"
+                               "r01_f32x2_issue_microbench.txt: 36.95 T lane-ops/s at 1965 MHz) x "
+                               "sampled SM clock / 1965",
+                "work": "reference operations per voxel-view over EXECUTED voxel-views only (%g "
+                        "sampling, %g load-free all-ones class, 0 for skipped tiles)" % (ops_s, ops_1),
+                "executed_voxel_views_per_step": executed_vv,
+                "executed_share": (pairs_s + pairs_1) / pairs_all,
+                "hbm_frac": achieved / hbm_peak, "ms_per_launch": fus_ms_per_launch,
+                "rank": rank}
+    tile_classes = {k: classes[k] / pairs_all for k in ("general", "inside", "all_ones", "all_kval",
+                                                         "outside")}
+
     line = {
         "metric": "carve_gvoxel_view_updates_per_s", "value": updates / (ms_step * 1e-3) / 1e9,
         "unit": "Gvoxel-view/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -360,15 +404,7 @@ def run_ours(args, cfg):
                        "owns) + vcb_sharded_extract_iso_count/_fill -> the whole mesh on rank 0's host",
                 "mesh_sha256": mesh_sha, "mesh_equals_1gpu_golden": mesh_sha_ok},
         "gpu_launches": int(round(launches_per_step * args.steps)),
-        "roofline": {"kernel": "fuse_kernel", "bound": "hbm", "achieved": achieved,
-                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                     "traffic": traffic, "peak_source": peak_src,
-                     "traffic_source": "ncu --set full capture of a 64-view launch, scaled to the "
-                                       "average views per launch (profiles/fuse_kernel_traffic.json)"
-                                       if traffic else None,
-                     "bytes_per_launch": bytes_per_launch, "ms_per_launch": fus_ms_per_launch,
-                     "note": "batched fusion is bound by instruction issue / the FP32 pipe, not by "
-                             "HBM (SURVEY.md 8d): see issue"},
+        "roofline": roofline,
         "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items()},
         "mc": {"ms": stages["marching_cubes"][0] / args.steps,
                "gvoxel_per_s": nvox / world / (stages["marching_cubes"][0] / args.steps * 1e-3) / 1e9,
@@ -381,19 +417,8 @@ def run_ours(args, cfg):
         "fusion_gvv_per_s": updates / world / (fus_ms / args.steps * 1e-3) / 1e9,
         "per_rank": per_rank,
     }
-    # for batched fusion the binding roofline is FP32 issue, not HBM.  Algorithmic
-    # operations per voxel-view in the reference's op order (54 weighted / 48 kMax) against the
-    # scalar FP32 lane rate; voxel-views the tile classes skip are counted as full, so the fraction
-    # is an upper bound on useful work and can exceed 1.  `issue` is what ncu measured on the kernel.
-    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-    ops = 54.0 if cfg["weighted"] else 48.0
-    peak_ops = 148 * 128 * sm_mhz * 1e6
-    line["fp32"] = {"ops_per_voxel_view": ops, "achieved_tops": updates / world * ops /
-                    (fus_ms / args.steps * 1e-3) / 1e12, "peak_tops": peak_ops / 1e12,
-                    "frac": updates / world * ops / (fus_ms / args.steps * 1e-3) / peak_ops,
-                    "note": "algorithmic ops of the reference per voxel-view / scalar FP32 lane "
-                            "rate; skipped voxel-views counted as full (upper bound)"}
-    line["roofline"]["binding"] = "fp32 issue (see fp32, issue)"
+    line["hbm"] = hbm
+    line["tile_classes"] = tile_classes
     line["issue"] = issue
     if world == 1 and not args.no_cpu_baseline:
         try:

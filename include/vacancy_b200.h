@@ -268,8 +268,26 @@ int vcb_extract_voxel_occupancy(vcb_carver* c, uint8_t* flags);
  * VCB_ERR_UNSUPPORTED. */
 int vcb_download_grid(vcb_carver* c, float* sdf, int32_t* update_num);
 int vcb_upload_grid(vcb_carver* c, const float* sdf, const int32_t* update_num);
+/* Grid checkpoint, no counterpart in the reference (it never serialises the grid): the owned
+ * slab's sdf[] and update_num[] with a header (grid size, plane range, carving options) in one raw
+ * file.  vcb_load_grid copies the planes that the file and this carver's slab share (any slab
+ * partition may restore any other; *planes_loaded tells how many) and refuses files of another grid
+ * or other carving options with VCB_ERR_INVALID.  Carving on after a restore gives the same bits as
+ * never having stopped.  For a multi-GPU grid vcb_sharded_save_grid writes one file per slab,
+ * "<prefix>.z<begin>-<end>.vcbgrid", and vcb_sharded_load_grid restores from a list of files that
+ * together cover the grid. */
+int vcb_save_grid(vcb_carver* c, const char* path);
+int vcb_load_grid(vcb_carver* c, const char* path, int32_t* planes_loaded);
 /* DEVICE pointers to the owned slab's state (stream-ordered access only). */
 int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev);
+
+/* Measurement aid, no counterpart in the reference: how the fusion kernel treated the (voxel tile,
+ * view) pairs of every launch since the last call.  A tile is 32 x 8 x 8 voxels (*voxels_per_tile);
+ * pairs[] counts, in this order: general path (sampling with per-voxel range tests), all texels
+ * 1.0f (load-free path), all texels kVal (view skipped: every sample would fail the truncation test
+ * of voxel_carver.cc:478-480), projection strictly inside the ROI (sampling without range tests),
+ * projection outside the ROI (skipped, voxel_carver.cc:462-472).  Calling it synchronises. */
+int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile);
 
 /* ---- one grid across several GPUs (z slabs) ---------------------------------------------------
  * No counterpart in the reference, which is single-process and single-device: a vcb_sharded stands
@@ -344,6 +362,8 @@ int vcb_sharded_local_mesh(vcb_sharded* s, int32_t i, int64_t* n_vertices, int64
  * process only - all cubes in the reference's raster order into host buffers. */
 int vcb_sharded_extract_voxel_count(vcb_sharded* s, int32_t inside_empty, int64_t* n_voxels);
 int vcb_sharded_extract_voxel_fill(vcb_sharded* s, float* vertices, int32_t* faces);
+int vcb_sharded_save_grid(vcb_sharded* s, const char* prefix);
+int vcb_sharded_load_grid(vcb_sharded* s, const char* const* paths, int32_t n_paths);
 /* vcb_stage_times of the i-th local slab (its 2D SDF share runs on a side stream, included). */
 int vcb_sharded_stage_times(vcb_sharded* s, int32_t i, float ms[4], int64_t launches[4]);
 

@@ -135,3 +135,55 @@ def test_engine_repartition_and_errors(cuda_lib, port):
     assert eng2._lib.vcb_sharded_extract_iso_fill(eng2._h, None, None) == -3
     with pytest.raises(Exception):
         sharded.LocalSlabs(o, 2, devices=[0, 99])
+
+
+def test_checkpoint_restore_then_carve_equals_uninterrupted(cuda_lib, port, tmp_path):
+    """vcb_save_grid / vcb_load_grid (and the vcb_sharded_* pair): carve 40 views on 3 slabs, save,
+    restore into (a) a single carver and (b) 2 slabs on other boundaries, carve 35 more views -
+    grid, update_num and mesh must equal the oracle's uninterrupted 75-view carve bit for bit.  In
+    weighted mode update_num is the running weight, so a wrong restore would show."""
+    o, opt, cams, masks = scene(n=64, views=75, size=160)
+    orc = oracle_carve(port, opt, cams, masks)
+    ws, wn = orc.download()
+    first = sharded.LocalSlabs(o, 3)
+    assert first.carve_batch(cams[:40], masks[:40])
+    paths = first.save_grid(tmp_path / "ckpt")
+    assert len(paths) == 3
+    first.close()
+    one = VoxelCarver(o)
+    assert one.Init()
+    assert sum(one.load_grid(p) for p in paths) == 64
+    assert one.carve_batch(cams[40:], masks[40:])
+    gs, gn = one.download_grid()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(one.ExtractIsoSurface(), orc.extract_iso(), o.bb_min, o.bb_max)
+    two = sharded.LocalSlabs(o, 2, ranges=[(0, 27), (27, 64)])
+    two.load_grid(paths)
+    assert two.carve_batch(cams[40:], masks[40:])
+    gs, gn = two.download_grid()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(two.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)
+    # files of another grid / other carving options, and incomplete sets, are refused
+    other = VoxelCarver(S.grid_option(32, weighted=True))
+    assert other.Init()
+    with pytest.raises(Exception, match="another grid"):
+        other.load_grid(paths[0])
+    kmax = VoxelCarver(S.grid_option(64, weighted=False))
+    assert kmax.Init()
+    with pytest.raises(Exception, match="another grid"):
+        kmax.load_grid(paths[0])
+    with pytest.raises(Exception, match="cover"):
+        sharded.LocalSlabs(o, 2).load_grid(paths[:2])
+
+
+def test_fusion_class_counts(cuda_lib):
+    """vcb_fusion_class_counts: every (tile, view) pair of every launch lands in exactly one class."""
+    o, opt, cams, masks = scene(n=64, views=70, size=256)
+    car = VoxelCarver(o)
+    assert car.Init() and car.carve_batch(cams, masks)
+    car.synchronize()
+    c = car.fusion_class_counts()
+    tiles = (64 // 32) * (64 // 8) * (64 // 8)
+    assert sum(c[k] for k in VoxelCarver.TILE_CLASSES) == tiles * 70
+    assert c["voxels_per_tile"] == 2048 and c["all_kval"] > 0 and c["all_ones"] > 0
+    assert sum(car.fusion_class_counts()[k] for k in VoxelCarver.TILE_CLASSES) == 0  # cleared

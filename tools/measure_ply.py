@@ -47,7 +47,7 @@ out = {"workload": wl, "vertices": nv, "faces": nf, "text_bytes": vb.value + fb.
        "gpu_lines_per_s": (nv + nf) / ((size_ms + fill_ms) * 1e-3)}
 try:
     ref = B.RefLib()
-    v, f = car.slab.mesh_host(nv, nf)
+    v, f = car.mesh_host()
     n = min(nv, 300000)
     with tempfile.TemporaryDirectory() as d:
         t0 = time.perf_counter()

@@ -410,6 +410,28 @@ class VoxelCarver:
         names = ("sdf2d", "fusion", "extract_voxel", "marching_cubes")
         return {k: (ms[i], n[i]) for i, k in enumerate(names)}
 
+    TILE_CLASSES = ("general", "all_ones", "all_kval", "inside", "outside")
+
+    def fusion_class_counts(self):
+        """How the fusion kernel treated the (voxel tile, view) pairs since the last call:
+        {class: pairs} plus "voxels_per_tile" (see vcb_fusion_class_counts)."""
+        pairs = (C.c_uint64 * 5)()
+        vpt = C.c_int64()
+        self._check(self._lib.vcb_fusion_class_counts(self._h, pairs, C.byref(vpt)))
+        out = {k: int(pairs[i]) for i, k in enumerate(self.TILE_CLASSES)}
+        out["voxels_per_tile"] = vpt.value
+        return out
+
+    def save_grid(self, path):
+        """Checkpoint of this carver's slab (vcb_save_grid)."""
+        self._check(self._lib.vcb_save_grid(self._h, str(path).encode()))
+
+    def load_grid(self, path):
+        """Restores the planes this slab shares with the file; returns how many."""
+        n = C.c_int32()
+        self._check(self._lib.vcb_load_grid(self._h, str(path).encode(), C.byref(n)))
+        return n.value
+
     def grid_device(self):
         a, b = C.c_void_p(), C.c_void_p()
         self._check(self._lib.vcb_grid_device(self._h, C.byref(a), C.byref(b)))

@@ -265,6 +265,11 @@ int flush_pending(vcb_carver* c) {
     Span span(c, 1);
     launch_fusion(c->fp, c->opt.sdf_interp, c->opt.voxel_update, c->stream, &c->stage_launches[1]);
   }
+  if (c->fp.tile_class == nullptr) {  // no classification: every (tile, view) pair took the general path
+    const uint64_t tiles = (uint64_t)((c->nx + 31) / 32) * ((c->ny + 7) / 8) *
+                           ((c->z_end - c->z_begin + 7) / 8);
+    c->unclassified_pairs += tiles * (uint64_t)c->pending;
+  }
   c->pending = 0;
   CU(c, cudaGetLastError());
   return VCB_OK;
@@ -526,6 +531,8 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
     CREATE_TRY(cudaMemcpy(*dpos[a], c->h_pos[a].data(), dims[a] * sizeof(float), cudaMemcpyHostToDevice));
   }
   CREATE_TRY(c->max_sdf.reserve(sizeof(float) * kMaxViewsPerLaunch));
+  CREATE_TRY(c->cls_counts.reserve(5 * sizeof(unsigned long long)));
+  CREATE_TRY(cudaMemset(c->cls_counts.ptr, 0, 5 * sizeof(unsigned long long)));
   // sdf = kVal, update_num = 0 (voxel_carver.cc:342, voxel_carver.h:67-68)
   launch_grid_reset(c);
   CREATE_TRY(cudaGetLastError());
@@ -544,6 +551,7 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
   c->fp.use_truncation = opt->use_truncation;
   c->fp.update_outside = opt->update_outside;
   c->fp.weight = opt->voxel_update_weight;
+  c->fp.class_counts = static_cast<unsigned long long*>(c->cls_counts.ptr);
 #undef CREATE_TRY
   {
     const int64_t cap = (int64_t)opt->voxel_max_update_num + 2;
@@ -576,7 +584,7 @@ void vcb_destroy(vcb_carver* c) {
   cudaFree(c->pos_y);
   cudaFree(c->pos_z);
   cudaFree(c->wtab);
-  Scratch* all[] = {&c->pool, &c->max_sdf, &c->tiles, &c->fuse_tabs, &c->ply.lens, &c->ply.tmp, &c->ply.text, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
+  Scratch* all[] = {&c->cls_counts, &c->pool, &c->max_sdf, &c->tiles, &c->fuse_tabs, &c->ply.lens, &c->ply.tmp, &c->ply.text, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
                     &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo};
@@ -1075,6 +1083,21 @@ int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev) {
   if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
   if (sdf_dev) *sdf_dev = c->sdf;
   if (update_num_dev) *update_num_dev = c->un;
+  return VCB_OK;
+}
+
+int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile) {
+  if (!c || !pairs) return fail(c, VCB_ERR_INVALID, "null argument");
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  unsigned long long h[5];
+  CU(c, cudaMemcpyAsync(h, c->cls_counts.ptr, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemsetAsync(c->cls_counts.ptr, 0, sizeof(h), c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  for (int k = 0; k < 5; k++) pairs[k] = h[k];
+  pairs[0] += c->unclassified_pairs;
+  c->unclassified_pairs = 0;
+  if (voxels_per_tile) *voxels_per_tile = 32 * 8 * 8;
   return VCB_OK;
 }
 

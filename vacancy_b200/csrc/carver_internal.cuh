@@ -40,6 +40,8 @@ struct vcb_carver {
   size_t slot_floats = 0;
   vcb::Scratch max_sdf;       // one float per slot
   vcb::Scratch fuse_tabs;     // per-launch tables of the fusion kernel (fusion_table_bytes)
+  vcb::Scratch cls_counts;    // 5 device counters: (tile, view) pairs per tile class (fusion.cu)
+  uint64_t unclassified_pairs = 0;  // pairs of launches that ran without tile classification
   vcb::PlyText ply;           // ASCII PLY text of the last extracted mesh (vcb_ply_body_*)
   vcb::Scratch tiles;         // 8x8-block flags per slot (tile_flag_bytes), see fusion.cu
   size_t tile_slot_bytes = 0;

@@ -75,6 +75,9 @@ struct FuseParams {
   const float4* view_tab;
   const float4* mz_tab;
   const unsigned char* tile_class;  // [fusion block][view], nullptr = every tile is "mixed"
+  // running totals of (tile, view) pairs per TileClass over all launches (device, 5 counters;
+  // read and cleared by vcb_fusion_class_counts) - what the tile classification actually skipped
+  unsigned long long* class_counts;
   FuseView views[kMaxViewsPerLaunch];
 };
 size_t fusion_table_bytes(int nx, int ny, int nz_slab);

@@ -227,6 +227,16 @@ class _Engine:
         self._check(self._lib.vcb_sharded_extract_voxel_count(self._h, int(inside_empty), C.byref(n)))
         return n.value
 
+    def save_grid(self, prefix):
+        """One checkpoint file per local slab: <prefix>.z<begin>-<end>.vcbgrid; returns the paths."""
+        self._check(self._lib.vcb_sharded_save_grid(self._h, str(prefix).encode()))
+        return ["%s.z%05d-%05d.vcbgrid" % (prefix, *self.ranges[r]) for r in self.local_ranks]
+
+    def load_grid(self, paths):
+        """Restores every local slab from checkpoint files that together cover it (any partition)."""
+        arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])
+        self._check(self._lib.vcb_sharded_load_grid(self._h, arr, len(paths)))
+
     def main_stream(self, i=0):
         """cudaStream_t (as an integer) that orders slab i's reset, fusion and extraction."""
         p = C.c_void_p()

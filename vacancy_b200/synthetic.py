@@ -74,4 +74,7 @@ CONFIGS = {
     "cfg3": dict(grid=512, views=100, image=2048, weighted=True),
     "cfg4": dict(grid=1024, views=360, image=2048, weighted=True),
     "cfg5": dict(grid=2048, views=720, image=2048, weighted=True),
+    # cfg4's geometry without truncation (kMax): no kVal / 1.0 plateaus in the SDF images, so every
+    # tile that projects into the image takes a sampling path - the fusion kernel's floor
+    "cfg4_nomask": dict(grid=1024, views=360, image=2048, weighted=False),
 }
