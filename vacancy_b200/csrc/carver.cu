@@ -587,7 +587,8 @@ void vcb_destroy(vcb_carver* c) {
   Scratch* all[] = {&c->cls_counts, &c->pool, &c->max_sdf, &c->tiles, &c->fuse_tabs, &c->ply.lens, &c->ply.tmp, &c->ply.text, &c->mask_stage, &c->sdf_scratch, &c->absmax, &c->vox.bits, &c->vox.segbase, &c->vox.tmp, &c->vox.stage,
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
-                    &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo};
+                    &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo,
+                    &c->iso.segwid, &c->iso.vb};
   for (Scratch* s : all) s->release();
   delete c;
 }

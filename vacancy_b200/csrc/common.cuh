@@ -173,7 +173,7 @@ cudaError_t ply_emit(const float* verts_dev, const int32_t* faces_dev, PlyText* 
 
 struct IsoExtract {
   Scratch ibits, vbits, cbits, abits, segcnt, segbase, active, tmp, hkeys, hvals, verts, faces,
-      counters, cinfo;
+      counters, cinfo, segwid, vb;
   int64_t n_vertices = -1, n_faces = -1;
   int phase = 0;          // 0 nothing, 1 counted, 2 vertices emitted, 3 faces emitted
   unsigned n_active = 0;  // active segments

@@ -38,6 +38,10 @@ namespace {
 __device__ uint64_t d_tri[256];       // packed triangle table, nibble i = edge of tri[i], 0xF = end
 __device__ uint16_t d_edge_mask[256]; // Bourke edgeTable, derived: edge flagged iff corners differ
 __device__ uint8_t d_ntri[256];
+// distinct edges of a configuration in the order the triangle walk first references them (i
+// ascending, j = 0..2 reading tri[i + 2 - j], marching_cubes.cc:199-218), one nibble each, 0xF ends:
+// the k-th OWNED edge of this list is the cube's k-th vertex
+__device__ uint64_t d_order[256];
 
 // corner k -> offset from the cube's max corner (marching_cubes.cc:93-101)
 __constant__ signed char c_corner[8][3] = {{-1, -1, -1}, {0, -1, -1}, {0, 0, -1}, {-1, 0, -1},
@@ -147,6 +151,8 @@ __global__ void __launch_bounds__(256) mc_ubits_kernel(const int32_t* __restrict
   }
 }
 
+constexpr unsigned kNoSlot = 0xffffffffu;  // segwid entry of a segment without active cubes
+
 // ---- bitmap pass --------------------------------------------------------------------------------
 // pair word: bit i = b[x] & b[x-1]   /  any word: bit i = b[x] | b[x-1]
 __device__ __forceinline__ unsigned shift_in(unsigned w, unsigned prev) {
@@ -157,7 +163,8 @@ __global__ void __launch_bounds__(256)
     mc_cube_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
                    const uint32_t* __restrict__ vbits, const uint32_t* __restrict__ ubits,
                    uint32_t* __restrict__ cbits, uint32_t* __restrict__ abits,
-                   uint32_t* __restrict__ active, unsigned* __restrict__ n_active) {
+                   uint32_t* __restrict__ active, unsigned* __restrict__ n_active,
+                   uint32_t* __restrict__ segwid) {
   const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= m.n_words) return;
   const int sx = (int)(w % m.spr);
@@ -184,11 +191,17 @@ __global__ void __launch_bounds__(256)
   if (z >= m.z_begin) {
     const int64_t seg = seg_index(m, sx, y, z);
     abits[seg] = a;
-    if (a) active[atomicAdd(n_active, 1u)] = (uint32_t)seg;
+    unsigned slot = kNoSlot;
+    if (a) {
+      slot = atomicAdd(n_active, 1u);
+      active[slot] = (uint32_t)seg;
+    }
+    segwid[seg] = slot;  // segment -> its place in the active list (the emit passes index by it)
   }
 }
 
 // ---- per-cube analysis --------------------------------------------------------------------------
+
 struct CubeInfo {
   int ci;          // cube index, marching_cubes.cc:121-128
   unsigned owned;  // crossed edges whose vertex this cube creates
@@ -272,6 +285,51 @@ __device__ __forceinline__ int32_t hash_find(const uint64_t* __restrict__ keys,
     if (k == kEmptyKey) return -1;
     slot = (slot + 1) & mask;
   }
+}
+
+// Where a vertex id is kept.  Among the <= 4 cubes sharing a grid edge the first in raster order
+// is the one whose max corner is the edge's upper endpoint - the edge's HOME cube, which sees it as
+// e6 (x-edge), e5 (y-edge) or e10 (z-edge).  When the home cube is non-skipped it owns the vertex,
+// and the id follows from what the emit passes keep per active cube anyway: the id of the cube's
+// first vertex (vb) and its configuration + owned-edge mask (cinfo) give
+//     id = vb[home] + (number of owned edges before it in the first-reference order).
+// Only vertices whose home cube is skipped or does not exist (next to kVal / un-updated voxels, on
+// the grid's low faces, or below this z slab) go through the hash table - in the interior of a
+// carved grid that is none.
+struct IdTables {
+  const uint32_t* cbits;
+  const uint32_t* segwid;  // owned segment -> slot in the active list
+  const uint32_t* cinfo;   // [slot][lane]: configuration | owned << 8
+  const int32_t* vb;       // [slot][lane]: global id of the cube's first vertex
+  const uint64_t* hkeys;
+  const int32_t* hvals;
+  uint64_t hmask;
+};
+
+__device__ __forceinline__ int owned_rank(int ci, unsigned owned, int e) {
+  const uint64_t ord = d_order[ci];
+  int r = 0;
+  for (int k = 0; k < 12; k++) {
+    const int ek = (int)((ord >> (4 * k)) & 0xF);
+    if (ek == e || ek == 0xF) break;
+    r += (int)((owned >> ek) & 1u);
+  }
+  return r;
+}
+
+// id of the vertex on the edge with upper endpoint (hx, hy, hz) along `axis` (-1: none)
+__device__ __forceinline__ int32_t vertex_id_of_edge(const McGeom& m, const IdTables& t, int hx,
+                                                     int hy, int hz, int axis) {
+  if (hz >= m.cz0 && cube_ok(t.cbits, m, hx, hy, hz)) {
+    const unsigned slot = t.segwid[seg_index(m, hx >> 5, hy, hz)];
+    const size_t at = (size_t)slot * 32 + (hx & 31);
+    const unsigned packed = t.cinfo[at];
+    const int e_home = axis == 0 ? 6 : (axis == 1 ? 5 : 10);
+    return t.vb[at] + owned_rank((int)(packed & 0xffu), (packed >> 8) & 0xfffu, e_home);
+  }
+  const uint64_t id = ((uint64_t)(hz - (axis == 2)) * m.ny + (hy - (axis == 1))) * m.nx +
+                      (hx - (axis == 0));
+  return hash_find(t.hkeys, t.hvals, t.hmask, (id << 2) | (uint64_t)axis);
 }
 
 __device__ __forceinline__ void seg_coords(const McGeom& m, int64_t seg, int* sx, int* y, int* z) {
@@ -361,8 +419,8 @@ __global__ void __launch_bounds__(128)
                      const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
                      const uint32_t* __restrict__ segcnt, const uint64_t* __restrict__ rowbase,
                      const uint32_t* __restrict__ cinfo, double iso, int linear_interp,
-                     int64_t vertex_offset, float* __restrict__ vertices, uint64_t* hkeys,
-                     int32_t* hvals, uint64_t hmask) {
+                     int64_t vertex_offset, float* __restrict__ vertices, int32_t* __restrict__ vb,
+                     uint64_t* hkeys, int32_t* hvals, uint64_t hmask) {
   const int lane = threadIdx.x & 31;
   const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (wid >= *n_active) return;
@@ -384,6 +442,7 @@ __global__ void __launch_bounds__(128)
   seg_base(m, seg, lane, segcnt, rowbase, &vbase, &fbase);
   if (nv == 0) return;
   int64_t vid = vbase + (inc - nv);
+  vb[(size_t)wid * 32 + lane] = (int32_t)(vid + vertex_offset);
   // corner values and positions
   const size_t plane = (size_t)m.nx * m.ny;
   float val[8], pos[8][3];
@@ -396,37 +455,35 @@ __global__ void __launch_bounds__(128)
     pos[k][1] = g.pos_y[cy];
     pos[k][2] = g.pos_z[cz];
   }
-  const uint64_t tri = d_tri[info.ci];
-  unsigned seen = 0;
-  for (int i = 0; i < 15 && ((tri >> (4 * i)) & 0xF) != 0xF; i += 3) {
-    for (int j = 0; j < 3; j++) {
-      const int e = (int)((tri >> (4 * (i + 2 - j))) & 0xF);
-      if ((seen >> e) & 1u) continue;
-      seen |= 1u << e;
-      if (!((info.owned >> e) & 1u)) continue;
-      const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
-      float p[3];
-      if (linear_interp) {
-        vertex_interp(iso, pos[a], pos[b], (double)val[a], (double)val[b], p);
-      } else {  // marching_cubes.cc:55
-        p[0] = pos[a][0]; p[1] = pos[a][1]; p[2] = pos[a][2];
-      }
-      vertices[vid * 3 + 0] = p[0];
-      vertices[vid * 3 + 1] = p[1];
-      vertices[vid * 3 + 2] = p[2];
-      hash_insert(hkeys, hvals, hmask, edge_key(m, x, y, z, e), (int32_t)(vid + vertex_offset));
-      vid++;
+  const uint64_t ord = d_order[info.ci];
+  for (int k = 0; k < 12; k++) {
+    const int e = (int)((ord >> (4 * k)) & 0xF);
+    if (e == 0xF) break;
+    if (!((info.owned >> e) & 1u)) continue;
+    const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
+    float p[3];
+    if (linear_interp) {
+      vertex_interp(iso, pos[a], pos[b], (double)val[a], (double)val[b], p);
+    } else {  // marching_cubes.cc:55
+      p[0] = pos[a][0]; p[1] = pos[a][1]; p[2] = pos[a][2];
     }
+    vertices[vid * 3 + 0] = p[0];
+    vertices[vid * 3 + 1] = p[1];
+    vertices[vid * 3 + 2] = p[2];
+    // e5 / e6 / e10 end in this cube's own max corner: this is their home cube and the id follows
+    // from vb + rank (vertex_id_of_edge); any other owned edge means its home cube is skipped
+    if (e != 5 && e != 6 && e != 10) {
+      hash_insert(hkeys, hvals, hmask, edge_key(m, x, y, z, e), (int32_t)(vid + vertex_offset));
+    }
+    vid++;
   }
 }
 
 __global__ void __launch_bounds__(128)
-    mc_face_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
-                   const uint32_t* __restrict__ abits, const uint32_t* __restrict__ active,
+    mc_face_kernel(const McGeom m, const uint32_t* __restrict__ active,
                    const unsigned* __restrict__ n_active, const uint32_t* __restrict__ segcnt,
-                   const uint64_t* __restrict__ rowbase, const uint32_t* __restrict__ cinfo,
-                   int32_t* __restrict__ faces, const uint64_t* __restrict__ hkeys,
-                   const int32_t* __restrict__ hvals, uint64_t hmask) {
+                   const uint64_t* __restrict__ rowbase, const IdTables t,
+                   int32_t* __restrict__ faces) {
   const int lane = threadIdx.x & 31;
   const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (wid >= *n_active) return;
@@ -434,14 +491,14 @@ __global__ void __launch_bounds__(128)
   int sx, y, z;
   seg_coords(m, seg, &sx, &y, &z);
   const int x = sx * 32 + lane;
-  const unsigned packed = cinfo[(size_t)wid * 32 + lane];
+  const unsigned packed = t.cinfo[(size_t)wid * 32 + lane];
   const bool act = packed != 0;
   const int ci = (int)(packed & 0xffu);
   const unsigned nt = act ? d_ntri[ci] : 0;
   unsigned inc = nt;
   for (int o = 1; o < 32; o <<= 1) {
-    const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += t;
+    const unsigned s = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += s;
   }
   int64_t vbase, fbase;
   seg_base(m, seg, lane, segcnt, rowbase, &vbase, &fbase);
@@ -453,13 +510,18 @@ __global__ void __launch_bounds__(128)
   while (em) {
     const int e = __ffs(em) - 1;
     em &= em - 1;
-    vid[e] = hash_find(hkeys, hvals, hmask, edge_key(m, x, y, z, e));
+    const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
+    const int hx = x + max(c_corner[a][0], c_corner[b][0]);
+    const int hy = y + max(c_corner[a][1], c_corner[b][1]);
+    const int hz = z + max(c_corner[a][2], c_corner[b][2]);
+    const int axis = c_corner[a][0] != c_corner[b][0] ? 0 : (c_corner[a][1] != c_corner[b][1] ? 1 : 2);
+    vid[e] = vertex_id_of_edge(m, t, hx, hy, hz, axis);
   }
   const uint64_t tri = d_tri[ci];
-  for (unsigned t = 0; t < nt; t++) {
+  for (unsigned k = 0; k < nt; k++) {
 #pragma unroll
     for (int j = 0; j < 3; j++) {  // face[j] = vertex of edge tri[i + (2 - j)], :202-204
-      const int e = (int)((tri >> (4 * (3 * t + 2 - j))) & 0xF);
+      const int e = (int)((tri >> (4 * (3 * k + 2 - j))) & 0xF);
       faces[fid * 3 + j] = vid[e];
     }
     fid++;
@@ -486,6 +548,23 @@ void init_mc_tables() {
     while (n < 5 && ((h_tri[c] >> (12 * n)) & 0xF) != 0xF) n++;
     nt[c] = (uint8_t)n;
   }
+  uint64_t order[256];
+  for (int c = 0; c < 256; c++) {
+    uint64_t o = 0;
+    unsigned seen = 0;
+    int k = 0;
+    for (int i = 0; i < 15 && ((h_tri[c] >> (4 * i)) & 0xF) != 0xF; i += 3) {
+      for (int j = 0; j < 3; j++) {
+        const unsigned e = (unsigned)((h_tri[c] >> (4 * (i + 2 - j))) & 0xF);
+        if ((seen >> e) & 1u) continue;
+        seen |= 1u << e;
+        o |= (uint64_t)e << (4 * k++);
+      }
+    }
+    for (; k < 16; k++) o |= (uint64_t)0xF << (4 * k);
+    order[c] = o;
+  }
+  cudaMemcpyToSymbol(d_order, order, sizeof(order));
   cudaMemcpyToSymbol(d_tri, h_tri, sizeof(h_tri));
   cudaMemcpyToSymbol(d_edge_mask, em, sizeof(em));
   cudaMemcpyToSymbol(d_ntri, nt, sizeof(nt));
@@ -504,15 +583,20 @@ namespace {
 // x- and y-edges lying in one voxel plane: id of the vertex on each (or -1). Used to hand the
 // vertices on a slab's top plane to the slab above it.
 __global__ void __launch_bounds__(256)
-    mc_export_plane_kernel(int nx, int ny, int z, const uint64_t* __restrict__ hkeys,
-                           const int32_t* __restrict__ hvals, uint64_t hmask,
-                           int32_t* __restrict__ out) {
+    mc_export_plane_kernel(const McGeom m, int z, const uint32_t* __restrict__ ibits,
+                           const IdTables t, int32_t* __restrict__ out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t n = (int64_t)nx * ny;
+  const int64_t n = (int64_t)m.nx * m.ny;
   if (i >= 2 * n) return;
   const int axis = (int)(i / n);
-  const uint64_t id = (uint64_t)z * n + (uint64_t)(i % n);  // lower endpoint of the edge
-  out[i] = hkeys ? hash_find(hkeys, hvals, hmask, (id << 2) | (uint64_t)axis) : -1;
+  const int lx = (int)((i % n) % m.nx), ly = (int)((i % n) / m.nx);  // lower endpoint of the edge
+  const int hx = lx + (axis == 0), hy = ly + (axis == 1);
+  int32_t id = -1;
+  // a vertex can only sit on an edge whose endpoints lie on different sides of the iso level
+  if (hx < m.nx && hy < m.ny && get_bit(ibits, m, lx, ly, z) != get_bit(ibits, m, hx, hy, z)) {
+    id = vertex_id_of_edge(m, t, hx, hy, z, axis);
+  }
+  out[i] = id;
 }
 
 __global__ void __launch_bounds__(256)
@@ -532,6 +616,18 @@ __global__ void __launch_bounds__(256)
 
 #define VCB_TRY(x) \
   if ((e = (x)) != cudaSuccess) return e
+
+static IdTables id_tables(const IsoExtract* st) {
+  IdTables t;
+  t.cbits = static_cast<const uint32_t*>(st->cbits.ptr);
+  t.segwid = static_cast<const uint32_t*>(st->segwid.ptr);
+  t.cinfo = static_cast<const uint32_t*>(st->cinfo.ptr);
+  t.vb = static_cast<const int32_t*>(st->vb.ptr);
+  t.hkeys = static_cast<const uint64_t*>(st->hkeys.ptr);
+  t.hvals = static_cast<const int32_t*>(st->hvals.ptr);
+  t.hmask = st->hmask;
+  return t;
+}
 
 // Phase 1: classification, counts and the raster-order prefix sums. Leaves n_vertices / n_faces.
 cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int linear_interp,
@@ -554,6 +650,7 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
   VCB_TRY(st->segbase.reserve((size_t)(2 * n_rows_owned + 2) * sizeof(uint64_t)));
   VCB_TRY(st->active.reserve((size_t)m.n_segs * sizeof(uint32_t)));
   VCB_TRY(st->counters.reserve(256));
+  VCB_TRY(st->segwid.reserve((size_t)m.n_segs * sizeof(uint32_t)));
   uint32_t* ibits = static_cast<uint32_t*>(st->ibits.ptr);
   uint32_t* vbits = static_cast<uint32_t*>(st->vbits.ptr);
   uint32_t* cbits = static_cast<uint32_t*>(st->cbits.ptr);
@@ -580,7 +677,7 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
     if (launches) *launches += 1;
   }
   mc_cube_kernel<<<(unsigned)((m.n_words + 255) / 256), 256, 0, stream>>>(
-      m, ibits, vbits, ubits, cbits, abits, active, n_active);
+      m, ibits, vbits, ubits, cbits, abits, active, n_active, static_cast<uint32_t*>(st->segwid.ptr));
   VCB_TRY(cudaMemsetAsync(segcnt, 0, (size_t)m.n_segs * sizeof(uint32_t), stream));
   VCB_TRY(cudaMemsetAsync(rowcnt, 0, (size_t)n_rows_owned * sizeof(uint64_t), stream));
   if (launches) *launches += 1;
@@ -591,6 +688,7 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
   const unsigned wblocks = (h_active + 3) / 4;  // 4 warps per block
   if (h_active > 0) {
     VCB_TRY(st->cinfo.reserve((size_t)h_active * 32 * sizeof(uint32_t)));
+    VCB_TRY(st->vb.reserve((size_t)h_active * 32 * sizeof(int32_t)));
     mc_count_kernel<<<wblocks, 128, 0, stream>>>(
         m, ibits, cbits, abits, active, n_active, segcnt,
         reinterpret_cast<unsigned long long*>(rowcnt), static_cast<uint32_t*>(st->cinfo.ptr));
@@ -633,7 +731,8 @@ cudaError_t iso_emit_vertices(const GridDesc& g, int64_t vertex_offset, IsoExtra
         static_cast<uint32_t*>(st->abits.ptr), static_cast<uint32_t*>(st->active.ptr),
         static_cast<unsigned*>(st->counters.ptr), static_cast<uint32_t*>(st->segcnt.ptr),
         static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin),
-        static_cast<uint32_t*>(st->cinfo.ptr), st->iso_level, st->linear_interp, vertex_offset, static_cast<float*>(st->verts.ptr),
+        static_cast<uint32_t*>(st->cinfo.ptr), st->iso_level, st->linear_interp, vertex_offset,
+        static_cast<float*>(st->verts.ptr), static_cast<int32_t*>(st->vb.ptr),
         static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), st->hmask);
     if (launches) *launches += 1;
   }
@@ -646,8 +745,7 @@ cudaError_t iso_export_top_ids(const GridDesc& g, IsoExtract* st, int32_t* out_d
   if (st->phase < 2) return cudaErrorInvalidValue;
   const int64_t n2 = 2ll * g.nx * g.ny;
   mc_export_plane_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, stream>>>(
-      g.nx, g.ny, g.z_end - 1, static_cast<uint64_t*>(st->hkeys.ptr),
-      static_cast<int32_t*>(st->hvals.ptr), st->hmask, out_dev);
+      mc_geom(g), g.z_end - 1, static_cast<uint32_t*>(st->ibits.ptr), id_tables(st), out_dev);
   if (launches) *launches += 1;
   return cudaGetLastError();
 }
@@ -670,12 +768,10 @@ cudaError_t iso_emit_faces(const GridDesc& g, IsoExtract* st, cudaStream_t strea
   const McGeom m = mc_geom(g);
   if (st->n_active > 0 && st->n_faces > 0) {
     mc_face_kernel<<<(st->n_active + 3) / 4, 128, 0, stream>>>(
-        m, static_cast<uint32_t*>(st->ibits.ptr), static_cast<uint32_t*>(st->abits.ptr),
-        static_cast<uint32_t*>(st->active.ptr), static_cast<unsigned*>(st->counters.ptr),
+        m, static_cast<uint32_t*>(st->active.ptr), static_cast<unsigned*>(st->counters.ptr),
         static_cast<uint32_t*>(st->segcnt.ptr),
         static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin),
-        static_cast<uint32_t*>(st->cinfo.ptr), static_cast<int32_t*>(st->faces.ptr),
-        static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), st->hmask);
+        id_tables(st), static_cast<int32_t*>(st->faces.ptr));
     if (launches) *launches += 1;
   }
   st->phase = 3;

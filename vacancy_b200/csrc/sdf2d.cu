@@ -96,23 +96,13 @@ __device__ __forceinline__ unsigned roi_word_mask(int x0, int rx0, int rx1) {
   return (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
 }
 
-// ---- pass 0: foreground bit-plane. One thread per 32-pixel word of a ROI row. -------------------
+// ---- foreground bits of 32 pixels of row y starting at x0 = 32 * w, ROI applied -----------------
 // Only the value 255 is foreground (voxel_carver.cc:109).
-__global__ void __launch_bounds__(256) sdf_bits_kernel(const __grid_constant__ SdfBatch B) {
-  const SdfView& v = B.v[blockIdx.y];
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    *v.absmax = 0;
-    *v.max_out = -FLT_MAX;
-  }
-  const int wpr = sdf_pitch(v.width) / 32;
-  const int rows = v.ry1 - v.ry0 + 1;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= rows * wpr) return;
-  const int y = v.ry0 + idx / wpr, w = idx % wpr;
+__device__ __forceinline__ unsigned mask_word(const SdfView& v, int y, int w) {
   const int x0 = w * 32;
   const uint8_t* __restrict__ m = v.mask + (size_t)y * v.width + x0;
   unsigned f = 0;
-  if ((v.width & 3) == 0 && x0 + 32 <= v.width) {
+  if ((v.width & 3) == 0 && (reinterpret_cast<size_t>(v.mask) & 3) == 0 && x0 + 32 <= v.width) {
     // byte == 0xFF  <=>  bit 7 set and the low 7 bits + 1 carry into bit 7; gather the four flags
     const uint32_t* __restrict__ m4 = reinterpret_cast<const uint32_t*>(m);
 #pragma unroll
@@ -126,10 +116,12 @@ __global__ void __launch_bounds__(256) sdf_bits_kernel(const __grid_constant__ S
       if (x0 + i < v.width && m[i] == 255) f |= 1u << i;
     }
   }
-  view_bits(v)[(size_t)y * wpr + w] = f & roi_word_mask(x0, v.rx0, v.rx1);
+  return f & roi_word_mask(x0, v.rx0, v.rx1);
 }
 
 // ---- pass 1: signed distance along the row. One warp per ROI row, one lane per 32-pixel word. ---
+// The lane builds its word of the foreground bit-plane straight from the mask bytes (the words of
+// the row stay in shared memory for the second sweep; no bit-plane goes through global memory).
 // For every ROI pixel: distance to the nearest pixel of the OTHER class in its row (inside the ROI):
 // negative on foreground, positive on background, +-kRowInf when the row has none.
 constexpr int kRowWarps = 8;
@@ -138,22 +130,27 @@ constexpr int kMaxWordsPerRow = kMaxImageDim / 32;
 __global__ void __launch_bounds__(kRowWarps * 32) sdf_row_kernel(const __grid_constant__ SdfBatch B) {
   const SdfView& v = B.v[blockIdx.y];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // cells the later passes accumulate into
+    *v.absmax = 0;
+    *v.max_out = -FLT_MAX;
+  }
   const int y = v.ry0 + blockIdx.x * kRowWarps + wib;
   if (y > v.ry1) return;
-  const int pitch = sdf_pitch(v.width), wpr = pitch / 32;
-  const uint32_t* __restrict__ bits = view_bits(v) + (size_t)y * wpr;
+  const int pitch = sdf_pitch(v.width);
   int16_t* __restrict__ out = view_rowd(v) + (size_t)y * pitch;
   const int w0 = v.rx0 >> 5, w1 = v.rx1 >> 5;
   constexpr int kFar = 1 << 20;
   // position of the last foreground / background pixel strictly before each word
   __shared__ int s_last_f[kRowWarps][kMaxWordsPerRow], s_last_b[kRowWarps][kMaxWordsPerRow];
+  __shared__ unsigned s_bits[kRowWarps][kMaxWordsPerRow];
 
   int carry_f = -kFar, carry_b = -kFar;
   for (int wb = w0; wb <= w1; wb += 32) {
     const int w = wb + lane;
     const bool ok = w <= w1;
     const unsigned vm = ok ? roi_word_mask(w * 32, v.rx0, v.rx1) : 0u;
-    const unsigned fw = ok ? bits[w] : 0u, bw = ~fw & vm;
+    const unsigned fw = ok ? mask_word(v, y, w) : 0u, bw = ~fw & vm;
+    if (ok) s_bits[wib][w - w0] = fw;
     int hf = fw ? w * 32 + 31 - __clz(fw) : -kFar;
     int hb = bw ? w * 32 + 31 - __clz(bw) : -kFar;
 #pragma unroll
@@ -184,7 +181,7 @@ __global__ void __launch_bounds__(kRowWarps * 32) sdf_row_kernel(const __grid_co
     const int w = w0 + c * 32 + lane;
     const bool ok = w <= w1;
     const unsigned vm = ok ? roi_word_mask(w * 32, v.rx0, v.rx1) : 0u;
-    const unsigned fw = ok ? bits[w] : 0u, bw = ~fw & vm;
+    const unsigned fw = ok ? s_bits[wib][w - w0] : 0u, bw = ~fw & vm;
     int lf = fw ? w * 32 + __ffs(fw) - 1 : 2 * kFar;
     int lb = bw ? w * 32 + __ffs(bw) - 1 : 2 * kFar;
 #pragma unroll
@@ -789,7 +786,6 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
     max_dist_bound = max(max_dist_bound, v.width + v.height);
     max_lut = max(max_lut, sdf_lut_entries(v.width, v.height));
   }
-  sdf_bits_kernel<<<dim3((max_words + 255) / 256, n_views), 256, 0, stream>>>(views_dev);
   sdf_row_kernel<<<dim3((max_rows + kRowWarps - 1) / kRowWarps, n_views), kRowWarps * 32, 0,
                    stream>>>(views_dev);
   const int max_seglen = (max_rows + 31) / 32;
@@ -819,7 +815,7 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
   }
   sdf_finalize_kernel<<<dim3((max_h + kTilePx - 1) / kTilePx, n_views), 256, 0, stream>>>(
       views_dev, mode, normalize, truncate, band);
-  if (launches) *launches += 4;
+  if (launches) *launches += 3;
 }
 
 void launch_sdf_color(const float* sdf, int64_t n, float min_neg, float max_pos, uint8_t* rgb,
