@@ -415,6 +415,18 @@ class PortLib:
     def carver(self, opt):
         return _PortCarver(self, opt)
 
+    def slab_carver(self, opt, z_begin, z_end):
+        """Planes [z_begin, z_end) of the grid `opt` describes, with GLOBAL positions and 64-bit
+        linear indices: the checker for grids the reference cannot hold (its ids are int,
+        voxel_carver.cc:298-301,307,333).  SURVEY.md section 8(c), last row."""
+        return _PortSlabCarver(self, opt, z_begin, z_end)
+
+
+def _shifted(arr, elements, ptr_type):
+    """Pointer `elements` items BEFORE arr[0]: lets C code that indexes with global linear ids
+    (size_t, z * nx * ny + ...) work on an array that holds only the planes from some z on."""
+    return C.cast(C.c_void_p(arr.ctypes.data - elements * arr.itemsize), ptr_type)
+
 
 class _PortCarver:
     def __init__(self, lib, opt):
@@ -504,3 +516,67 @@ class _PortCarver:
                                      C.c_float(self.opt.resolution), _p(flags, c_u8_p),
                                      _p(v, c_float_p), _p(f, c_int_p))
         return v, f
+
+
+class _PortSlabCarver(_PortCarver):
+    """_PortCarver restricted to the planes [z_begin, z_end): same C functions, same global
+    positions; the state arrays hold only the slab and are addressed through shifted pointers."""
+
+    def __init__(self, lib, opt, z_begin, z_end):
+        self.lib, self.L, self.opt = lib, lib.L, opt
+        d = np.zeros(3, np.int32)
+        if not self.L.vo_grid_dims(C.byref(opt), _p(d, c_int_p)):
+            raise ValueError("oracle: Init() would return false")
+        self._d = d
+        self.dims = tuple(int(v) for v in d)
+        assert 0 <= z_begin < z_end <= self.dims[2]
+        self.z_begin, self.z_end = int(z_begin), int(z_end)
+        self.plane = self.dims[0] * self.dims[1]
+        self.count = self.plane * (self.z_end - self.z_begin)
+        self.px, self.py, self.pz = (np.zeros(n, np.float32) for n in self.dims)
+        self.L.vo_grid_positions(C.byref(opt), _p(self.px, c_float_p), _p(self.py, c_float_p),
+                                 _p(self.pz, c_float_p))
+        self.sdf = np.empty(self.count, np.float32)
+        self.un = np.empty(self.count, np.int32)
+        self.L.vo_grid_reset(_p(self.sdf, c_float_p), _p(self.un, c_int_p), self.count)
+
+    def carve_sdf(self, cam, sdf, roi=None, z_range=None):
+        sdf = np.ascontiguousarray(sdf, np.float32)
+        h, w = sdf.shape
+        roi = roi or (0, 0, w - 1, h - 1)
+        v = self.view(cam, roi)
+        v.width, v.height = w, h
+        shift = self.z_begin * self.plane  # first global linear id of the slab (may exceed 2^31)
+        self.L.vo_carve_sdf(C.byref(self.opt), _p(self._d, c_int_p), _p(self.px, c_float_p),
+                            _p(self.py, c_float_p), _p(self.pz, c_float_p), self.z_begin,
+                            self.z_end, C.byref(v), _p(sdf, c_float_p),
+                            _shifted(self.sdf, shift, c_float_p), _shifted(self.un, shift, c_int_p))
+
+    def _sub(self):
+        """(dims, pz) of the slab seen as a grid of its own (positions stay the global ones)."""
+        d = np.array([self.dims[0], self.dims[1], self.z_end - self.z_begin], np.int32)
+        return d, np.ascontiguousarray(self.pz[self.z_begin:self.z_end])
+
+    def extract_iso(self, iso=0.0, interp=True, timing=None):
+        """Marching cubes over the slab alone (no planes below it): what a z-slab carver whose halo
+        holds kVal extracts, numbered from 0."""
+        d, pz = self._sub()
+        vp, fp = c_float_p(), c_int_p()
+        nv, nf = C.c_int64(), C.c_int64()
+        self.L.vo_marching_cubes(_p(d, c_int_p), _p(self.px, c_float_p), _p(self.py, c_float_p),
+                                 _p(pz, c_float_p), _p(self.sdf, c_float_p), _p(self.un, c_int_p),
+                                 iso, int(interp), C.byref(vp), C.byref(nv), C.byref(fp),
+                                 C.byref(nf))
+        v = np.ctypeslib.as_array(vp, shape=(max(nv.value, 1), 3))[:nv.value].copy()
+        f = np.ctypeslib.as_array(fp, shape=(max(nf.value, 1), 3))[:nf.value].copy()
+        self.L.vo_free(vp)
+        self.L.vo_free(fp)
+        return v, f
+
+    def occupancy(self, inside_empty=False):
+        d, _ = self._sub()
+        flags = np.empty(self.count, np.uint8)
+        n = self.L.vo_extract_voxel_flags(_p(d, c_int_p), _p(self.sdf, c_float_p),
+                                          _p(self.un, c_int_p), int(inside_empty),
+                                          _p(flags, c_u8_p))
+        return flags, int(n)

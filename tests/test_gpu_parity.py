@@ -68,11 +68,15 @@ def test_sdf2d_bunny_and_large(cuda_lib, port, bunny):
     ((16384, 64), (5, 3000, 60, 6100)),        # tall, ROI of 3101 rows (<= 3168): same kernel, partial ROI
     ((5000, 12000), None),                     # 5000 rows > 3168: the three-sweep column pass
     ((5000, 12000), (100, 200, 11000, 4900)),  # same, partial ROI (4701 rows)
+    ((3500, 300), None),                       # packed pass, but too tall for the on-chip strip
+    ((1400, 500), (7, 9, 450, 1390)),          # packed pass, 64-column strip, odd ROI origin
 ])
-def test_sdf2d_large_images_take_the_int32_column_passes(cuda_lib, port, shape, roi):
-    """Images with width + height > 16000 leave the packed 16-bit column pass (sdf_col_pack_kernel)
-    for sdf_col_smem_kernel (ROI height <= 3168) or sdf_col_kernel; both must stay bit-exact, with
-    columns that are all foreground / all background inside the ROI (no seed in the column)."""
+def test_sdf2d_every_column_pass_variant(cuda_lib, port, shape, roi):
+    """Images with width + height > 16000 leave the packed 16-bit column pass for
+    sdf_col_smem_kernel (ROI height <= 3168) or sdf_col_kernel; smaller ones take the packed pass
+    with its forward strip in shared memory (64 or 32 columns per block) or, when too tall for that,
+    through global memory (sdf_col_pack_kernel).  All must stay bit-exact, with columns that are all
+    foreground / all background inside the ROI (no seed in the column)."""
     h, w = shape
     rng = np.random.default_rng(h * 7 + w)
     yy, xx = np.mgrid[0:h, 0:w]
@@ -394,6 +398,41 @@ def test_cfg4_slab_all_360_views_against_compiled_reference(cuda_lib, ref):
     H.assert_mesh_equal(car.ExtractIsoSurface(), rc.extract_iso(), opt.bb_min, opt.bb_max)
     flags, cnt = car.occupancy(False)
     assert cnt == int(((ws <= 0) & (wn >= 1)).sum())
+
+
+def test_cfg5_slab_with_linear_indices_beyond_2_31(cuda_lib, port):
+    """BASELINE.json config 5 (2048^3, 2048^2 views, weighted TSDF) cannot run on the reference: its
+    voxel ids are int (voxel_carver.cc:298-301,307,333).  The checker there is the 64-bit slab
+    restatement (oracle slab_carver: the same C functions as the whole-grid oracle, which is pinned
+    to the compiled reference, on planes addressed by their GLOBAL linear index).  Planes
+    [1100, 1116): the first voxel's linear id is 1100 * 2048^2 = 4.6e9 > 2^32, so positions, fusion
+    tables and the marching-cubes edge keys all work on 64-bit indices.  The slab's halo is left at
+    kVal (no lower neighbour), which makes its extraction the marching cubes of the slab alone."""
+    n, size, z0, z1 = 2048, 2048, 1100, 1116
+    assert z0 * n * n > 2 ** 32
+    o = S.grid_option(n, weighted=True)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True, band=0.1)
+    car = VoxelCarver(o, z_range=(z0, z1))
+    assert car.Init(), car.last_error
+    assert car.dims == (n, n, n) and car.z_range == (z0, z1)
+    all_cams = S.circle_cameras(S.CONFIGS["cfg5"]["views"], size)
+    cams = [all_cams[i] for i in (0, 97, 250, 431, 600)]
+    mask = S.silhouette(cams[0])
+    assert car.carve_batch(cams, [mask] * len(cams))
+    orc = port.slab_carver(opt, z0, z1)
+    sdf = port.make_sdf(mask, None, True, True, 0.1)
+    for c in cams:
+        orc.carve_sdf(H.to_oracle_camera(c), sdf)
+    px, py, pz = car.positions()
+    assert bits_equal(pz, orc.pz) and bits_equal(px, orc.px)
+    (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+    assert int(wn.max()) == len(cams) and np.array_equal(gn, wn) and bits_equal(gs, ws)
+    gv, gf = car.ExtractIsoSurface()
+    assert len(gv) > 10000
+    H.assert_mesh_equal((gv, gf), orc.extract_iso(), o.bb_min, o.bb_max)
+    flags, cnt = car.occupancy(False)
+    wflags, wcnt = orc.occupancy(False)
+    assert cnt == wcnt and np.array_equal(flags, wflags)
 
 
 def test_sdf_color_map(cuda_lib, port, bunny):

@@ -249,3 +249,23 @@ def test_euclidean_sdf_oracle_vs_scipy_and_brute_force(port):
                     e = np.finfo(np.float32).max
                 want[y, x] = -e if me else e
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_slab_oracle_equals_the_planes_of_the_whole_grid_oracle(port):
+    """The 64-bit slab restatement used where the reference overflows (config 5): on a grid small
+    enough for the whole-grid oracle - itself bit-identical to the compiled reference, above - the
+    slab carver must hold exactly the planes it covers, for grid state and occupancy."""
+    from vacancy_b200 import synthetic as S
+    o = S.grid_option(40, weighted=True)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True, band=0.1)
+    cams = S.circle_cameras(7, 120, tilt=0.3)
+    whole, slab = port.carver(opt), port.slab_carver(opt, 13, 29)
+    for c in cams:
+        m = S.silhouette(c, S.DUMBBELL)
+        whole.carve_mask(H.to_oracle_camera(c), m)
+        slab.carve_mask(H.to_oracle_camera(c), m)
+    (ws, wn), (ss, sn) = whole.download(), slab.download()
+    pl = 40 * 40
+    assert np.array_equal(ws[13 * pl:29 * pl].view(np.uint32), ss.view(np.uint32))
+    assert np.array_equal(wn[13 * pl:29 * pl], sn)
+    assert len(slab.extract_iso()[0]) > 0

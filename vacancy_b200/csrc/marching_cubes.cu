@@ -213,22 +213,45 @@ __device__ __forceinline__ unsigned cube_ok(const uint32_t* __restrict__ cbits, 
   return get_bit(cbits, m, x, y, z);
 }
 
+// Configuration and owned edges of the cube of lane `lane` in segment (sx, y, z).  Every lane of
+// the warp reads the same few bitmap words (broadcast loads): the rows (y-1, y) x (z-1, z) of the
+// inside bits for the 8 corners, and the rows of the cube-valid bits that hold the <= 9 earlier
+// cubes sharing an edge with this one; bit `lane` of a word shifted by one position is the
+// neighbour at x - 1 / x + 1.
+__device__ __forceinline__ unsigned shift_out(unsigned w, unsigned next) {
+  return (w >> 1) | (next << 31);
+}
+
 __device__ __forceinline__ CubeInfo cube_info(const McGeom& m, const uint32_t* __restrict__ ibits,
-                                              const uint32_t* __restrict__ cbits, int x, int y,
-                                              int z) {
-  CubeInfo info;
+                                              const uint32_t* __restrict__ cbits, int sx, int y,
+                                              int z, int lane) {
+  const int64_t w11 = word_index(m, sx, y, z);            // row (y, z)
+  const int64_t w01 = w11 - m.spr;                        // row (y - 1, z)
+  const int64_t w10 = w11 - (int64_t)m.spr * m.ny;        // row (y, z - 1)
+  const int64_t w00 = w10 - m.spr;                        // row (y - 1, z - 1)
+  const bool has_prev = sx > 0, has_next = sx + 1 < m.spr;
+  // inside bits: corner k of the cube at bit `lane`
+  const unsigned i00 = ibits[w00], i01 = ibits[w01], i10 = ibits[w10], i11 = ibits[w11];
+  const unsigned p00 = has_prev ? ibits[w00 - 1] : 0u, p01 = has_prev ? ibits[w01 - 1] : 0u;
+  const unsigned p10 = has_prev ? ibits[w10 - 1] : 0u, p11 = has_prev ? ibits[w11 - 1] : 0u;
+  const unsigned corner[8] = {shift_in(i00, p00), i00, i10, shift_in(i10, p10),
+                              shift_in(i01, p01), i01, i11, shift_in(i11, p11)};
   int ci = 0;
 #pragma unroll
-  for (int k = 0; k < 8; k++) {
-    ci |= (int)get_bit(ibits, m, x + c_corner[k][0], y + c_corner[k][1], z + c_corner[k][2]) << k;
-  }
+  for (int k = 0; k < 8; k++) ci |= (int)((corner[k] >> lane) & 1u) << k;
+  CubeInfo info;
   info.ci = ci;
-  // earlier cubes (raster order) that share an edge with this one
-  const unsigned n1 = cube_ok(cbits, m, x, y - 1, z - 1), n2 = cube_ok(cbits, m, x, y, z - 1);
-  const unsigned n3 = cube_ok(cbits, m, x, y + 1, z - 1), n4 = cube_ok(cbits, m, x - 1, y, z - 1);
-  const unsigned n5 = cube_ok(cbits, m, x + 1, y, z - 1), n6 = cube_ok(cbits, m, x, y - 1, z);
-  const unsigned n7 = cube_ok(cbits, m, x - 1, y, z), n8 = cube_ok(cbits, m, x - 1, y - 1, z);
-  const unsigned n9 = cube_ok(cbits, m, x + 1, y - 1, z);
+  // earlier cubes (raster order) that share an edge with this one; rows that do not exist and
+  // cubes outside the grid read as 0 (mc_cube_kernel leaves their bits clear)
+  const unsigned c00 = cbits[w00], c10 = cbits[w10], c01 = cbits[w01], c11 = cbits[w11];
+  const unsigned c20 = y + 1 < m.ny ? cbits[w10 + m.spr] : 0u;  // row (y + 1, z - 1)
+  const unsigned c10p = has_prev ? cbits[w10 - 1] : 0u, c10n = has_next ? cbits[w10 + 1] : 0u;
+  const unsigned c01p = has_prev ? cbits[w01 - 1] : 0u, c01n = has_next ? cbits[w01 + 1] : 0u;
+  const unsigned c11p = has_prev ? cbits[w11 - 1] : 0u;
+  const unsigned n1 = (c00 >> lane) & 1u, n2 = (c10 >> lane) & 1u, n3 = (c20 >> lane) & 1u;
+  const unsigned n4 = (shift_in(c10, c10p) >> lane) & 1u, n5 = (shift_out(c10, c10n) >> lane) & 1u;
+  const unsigned n6 = (c01 >> lane) & 1u, n7 = (shift_in(c11, c11p) >> lane) & 1u;
+  const unsigned n8 = (shift_in(c01, c01p) >> lane) & 1u, n9 = (shift_out(c01, c01n) >> lane) & 1u;
   unsigned taken = 0;  // edges already created by an earlier cube
   taken |= (n1 | n2 | n6) << 0;
   taken |= (n2 | n5) << 1;
@@ -289,43 +312,28 @@ __device__ __forceinline__ int32_t hash_find(const uint64_t* __restrict__ keys,
 
 // Where a vertex id is kept.  Among the <= 4 cubes sharing a grid edge the first in raster order
 // is the one whose max corner is the edge's upper endpoint - the edge's HOME cube, which sees it as
-// e6 (x-edge), e5 (y-edge) or e10 (z-edge).  When the home cube is non-skipped it owns the vertex,
-// and the id follows from what the emit passes keep per active cube anyway: the id of the cube's
-// first vertex (vb) and its configuration + owned-edge mask (cinfo) give
-//     id = vb[home] + (number of owned edges before it in the first-reference order).
-// Only vertices whose home cube is skipped or does not exist (next to kVal / un-updated voxels, on
-// the grid's low faces, or below this z slab) go through the hash table - in the interior of a
-// carved grid that is none.
+// e6 (x-edge), e5 (y-edge) or e10 (z-edge).  When the home cube is non-skipped it owns the vertex;
+// the vertex pass leaves, for every cube of every active segment, the ids of the (up to three)
+// vertices it is the home of: ids3[slot][lane][axis], -1 where it owns none.  Only vertices whose
+// home cube is skipped or does not exist (next to kVal / un-updated voxels, on the grid's low
+// faces, or below this z slab) go through the hash table - in the interior of a carved grid none.
 struct IdTables {
-  const uint32_t* cbits;
-  const uint32_t* segwid;  // owned segment -> slot in the active list
-  const uint32_t* cinfo;   // [slot][lane]: configuration | owned << 8
-  const int32_t* vb;       // [slot][lane]: global id of the cube's first vertex
+  const uint32_t* segwid;  // owned segment -> slot in the active list (kNoSlot: no active cube)
+  const int32_t* ids3;     // [slot][lane][axis]
   const uint64_t* hkeys;
   const int32_t* hvals;
   uint64_t hmask;
 };
 
-__device__ __forceinline__ int owned_rank(int ci, unsigned owned, int e) {
-  const uint64_t ord = d_order[ci];
-  int r = 0;
-  for (int k = 0; k < 12; k++) {
-    const int ek = (int)((ord >> (4 * k)) & 0xF);
-    if (ek == e || ek == 0xF) break;
-    r += (int)((owned >> ek) & 1u);
-  }
-  return r;
-}
-
 // id of the vertex on the edge with upper endpoint (hx, hy, hz) along `axis` (-1: none)
 __device__ __forceinline__ int32_t vertex_id_of_edge(const McGeom& m, const IdTables& t, int hx,
                                                      int hy, int hz, int axis) {
-  if (hz >= m.cz0 && cube_ok(t.cbits, m, hx, hy, hz)) {
+  if (hx >= 1 && hy >= 1 && hz >= m.cz0) {  // a cube of this slab
     const unsigned slot = t.segwid[seg_index(m, hx >> 5, hy, hz)];
-    const size_t at = (size_t)slot * 32 + (hx & 31);
-    const unsigned packed = t.cinfo[at];
-    const int e_home = axis == 0 ? 6 : (axis == 1 ? 5 : 10);
-    return t.vb[at] + owned_rank((int)(packed & 0xffu), (packed >> 8) & 0xfffu, e_home);
+    if (slot != kNoSlot) {
+      const int32_t id = t.ids3[((size_t)slot * 32 + (hx & 31)) * 3 + axis];
+      if (id >= 0) return id;
+    }
   }
   const uint64_t id = ((uint64_t)(hz - (axis == 2)) * m.ny + (hy - (axis == 1))) * m.nx +
                       (hx - (axis == 0));
@@ -375,7 +383,7 @@ __global__ void __launch_bounds__(128)
   seg_coords(m, seg, &sx, &y, &z);
   unsigned nv = 0, nt = 0, packed = 0;
   if ((abits[seg] >> lane) & 1u) {
-    const CubeInfo info = cube_info(m, ibits, cbits, sx * 32 + lane, y, z);
+    const CubeInfo info = cube_info(m, ibits, cbits, sx, y, z, lane);
     nv = __popc(info.owned);
     nt = d_ntri[info.ci];
     packed = (unsigned)info.ci | (info.owned << 8) | 0x80000000u;
@@ -419,8 +427,8 @@ __global__ void __launch_bounds__(128)
                      const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
                      const uint32_t* __restrict__ segcnt, const uint64_t* __restrict__ rowbase,
                      const uint32_t* __restrict__ cinfo, double iso, int linear_interp,
-                     int64_t vertex_offset, float* __restrict__ vertices, int32_t* __restrict__ vb,
-                     uint64_t* hkeys, int32_t* hvals, uint64_t hmask) {
+                     int64_t vertex_offset, float* __restrict__ vertices,
+                     int32_t* __restrict__ ids3, uint64_t* hkeys, int32_t* hvals, uint64_t hmask) {
   const int lane = threadIdx.x & 31;
   const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (wid >= *n_active) return;
@@ -440,50 +448,57 @@ __global__ void __launch_bounds__(128)
   }
   int64_t vbase, fbase;
   seg_base(m, seg, lane, segcnt, rowbase, &vbase, &fbase);
-  if (nv == 0) return;
+  // ids of the vertices on the three edges that end in this cube's max corner (e6 along x, e5 along
+  // y, e10 along z) - the edges this cube is the HOME of; -1 where it owns none (see IdTables)
+  int32_t home_id[3] = {-1, -1, -1};
   int64_t vid = vbase + (inc - nv);
-  vb[(size_t)wid * 32 + lane] = (int32_t)(vid + vertex_offset);
-  // corner values and positions
   const size_t plane = (size_t)m.nx * m.ny;
-  float val[8], pos[8][3];
-#pragma unroll
-  for (int k = 0; k < 8; k++) {
-    const int cx = x + c_corner[k][0], cy = y + c_corner[k][1], cz = z + c_corner[k][2];
-    // g.sdf points at plane z_begin; halo planes sit at negative offsets
-    val[k] = g.sdf[((ptrdiff_t)cz - g.z_begin) * (ptrdiff_t)plane + (ptrdiff_t)cy * m.nx + cx];
-    pos[k][0] = g.pos_x[cx];
-    pos[k][1] = g.pos_y[cy];
-    pos[k][2] = g.pos_z[cz];
-  }
-  const uint64_t ord = d_order[info.ci];
+  const uint64_t ord = nv ? d_order[info.ci] : ~0ull;
   for (int k = 0; k < 12; k++) {
     const int e = (int)((ord >> (4 * k)) & 0xF);
     if (e == 0xF) break;
     if (!((info.owned >> e) & 1u)) continue;
+    // the two end points of the edge, loaded on demand (most cubes own one or two vertices)
     const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
+    const int ax = x + c_corner[a][0], ay = y + c_corner[a][1], az = z + c_corner[a][2];
+    const int bx = x + c_corner[b][0], by = y + c_corner[b][1], bz = z + c_corner[b][2];
+    const float p1[3] = {g.pos_x[ax], g.pos_y[ay], g.pos_z[az]};
     float p[3];
     if (linear_interp) {
-      vertex_interp(iso, pos[a], pos[b], (double)val[a], (double)val[b], p);
+      const float p2[3] = {g.pos_x[bx], g.pos_y[by], g.pos_z[bz]};
+      // g.sdf points at plane z_begin; halo planes sit at negative offsets
+      const float v1 = g.sdf[((ptrdiff_t)az - g.z_begin) * (ptrdiff_t)plane + (ptrdiff_t)ay * m.nx + ax];
+      const float v2 = g.sdf[((ptrdiff_t)bz - g.z_begin) * (ptrdiff_t)plane + (ptrdiff_t)by * m.nx + bx];
+      vertex_interp(iso, p1, p2, (double)v1, (double)v2, p);
     } else {  // marching_cubes.cc:55
-      p[0] = pos[a][0]; p[1] = pos[a][1]; p[2] = pos[a][2];
+      p[0] = p1[0]; p[1] = p1[1]; p[2] = p1[2];
     }
     vertices[vid * 3 + 0] = p[0];
     vertices[vid * 3 + 1] = p[1];
     vertices[vid * 3 + 2] = p[2];
-    // e5 / e6 / e10 end in this cube's own max corner: this is their home cube and the id follows
-    // from vb + rank (vertex_id_of_edge); any other owned edge means its home cube is skipped
-    if (e != 5 && e != 6 && e != 10) {
-      hash_insert(hkeys, hvals, hmask, edge_key(m, x, y, z, e), (int32_t)(vid + vertex_offset));
+    const int32_t gid = (int32_t)(vid + vertex_offset);
+    if (e == 6) {
+      home_id[0] = gid;
+    } else if (e == 5) {
+      home_id[1] = gid;
+    } else if (e == 10) {
+      home_id[2] = gid;
+    } else {  // owned although another cube is its home: that cube is skipped or does not exist
+      hash_insert(hkeys, hvals, hmask, edge_key(m, x, y, z, e), gid);
     }
     vid++;
   }
+  int32_t* __restrict__ out = ids3 + ((size_t)wid * 32 + lane) * 3;
+  out[0] = home_id[0];
+  out[1] = home_id[1];
+  out[2] = home_id[2];
 }
 
 __global__ void __launch_bounds__(128)
     mc_face_kernel(const McGeom m, const uint32_t* __restrict__ active,
                    const unsigned* __restrict__ n_active, const uint32_t* __restrict__ segcnt,
-                   const uint64_t* __restrict__ rowbase, const IdTables t,
-                   int32_t* __restrict__ faces) {
+                   const uint64_t* __restrict__ rowbase, const uint32_t* __restrict__ cinfo,
+                   const IdTables t, int32_t* __restrict__ faces) {
   const int lane = threadIdx.x & 31;
   const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (wid >= *n_active) return;
@@ -491,7 +506,7 @@ __global__ void __launch_bounds__(128)
   int sx, y, z;
   seg_coords(m, seg, &sx, &y, &z);
   const int x = sx * 32 + lane;
-  const unsigned packed = t.cinfo[(size_t)wid * 32 + lane];
+  const unsigned packed = cinfo[(size_t)wid * 32 + lane];
   const bool act = packed != 0;
   const int ci = (int)(packed & 0xffu);
   const unsigned nt = act ? d_ntri[ci] : 0;
@@ -619,10 +634,8 @@ __global__ void __launch_bounds__(256)
 
 static IdTables id_tables(const IsoExtract* st) {
   IdTables t;
-  t.cbits = static_cast<const uint32_t*>(st->cbits.ptr);
   t.segwid = static_cast<const uint32_t*>(st->segwid.ptr);
-  t.cinfo = static_cast<const uint32_t*>(st->cinfo.ptr);
-  t.vb = static_cast<const int32_t*>(st->vb.ptr);
+  t.ids3 = static_cast<const int32_t*>(st->vb.ptr);
   t.hkeys = static_cast<const uint64_t*>(st->hkeys.ptr);
   t.hvals = static_cast<const int32_t*>(st->hvals.ptr);
   t.hmask = st->hmask;
@@ -688,7 +701,7 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
   const unsigned wblocks = (h_active + 3) / 4;  // 4 warps per block
   if (h_active > 0) {
     VCB_TRY(st->cinfo.reserve((size_t)h_active * 32 * sizeof(uint32_t)));
-    VCB_TRY(st->vb.reserve((size_t)h_active * 32 * sizeof(int32_t)));
+    VCB_TRY(st->vb.reserve((size_t)h_active * 32 * 3 * sizeof(int32_t)));
     mc_count_kernel<<<wblocks, 128, 0, stream>>>(
         m, ibits, cbits, abits, active, n_active, segcnt,
         reinterpret_cast<unsigned long long*>(rowcnt), static_cast<uint32_t*>(st->cinfo.ptr));
@@ -771,7 +784,7 @@ cudaError_t iso_emit_faces(const GridDesc& g, IsoExtract* st, cudaStream_t strea
         m, static_cast<uint32_t*>(st->active.ptr), static_cast<unsigned*>(st->counters.ptr),
         static_cast<uint32_t*>(st->segcnt.ptr),
         static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin),
-        id_tables(st), static_cast<int32_t*>(st->faces.ptr));
+        static_cast<uint32_t*>(st->cinfo.ptr), id_tables(st), static_cast<int32_t*>(st->faces.ptr));
     if (launches) *launches += 1;
   }
   st->phase = 3;

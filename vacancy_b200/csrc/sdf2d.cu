@@ -506,6 +506,96 @@ __global__ void __launch_bounds__(32 * kPackSegs, 2)
   if (lane == 0 && local_max > 0) atomicMax(v.absmax, local_max);
 }
 
+// ---- pass 2, packed, forward results kept on chip ----------------------------------------------
+// The same two sweeps as sdf_col_pack_kernel, but the block's strip (2 * kLanes columns x all ROI
+// rows) of forward results stays in shared memory between the sweeps instead of going out to the
+// int16 plane and back: the row distances are read once and the final distances written once.
+// kLanes = 32: 64 columns x 16 row segments (ROI heights up to ~1500 rows); kLanes = 16: 32 columns
+// x 32 segments (up to ~3000 rows; a warp then covers two segments of 16 lanes, 64-byte accesses).
+template <int kLanes>
+__global__ void __launch_bounds__(512, 1)
+    sdf_col_pack_smem_kernel(const __grid_constant__ SdfBatch B, int seglen_max) {
+  constexpr int kSegs = 512 / kLanes;
+  const SdfView& v = B.v[blockIdx.y];
+  const int lane = threadIdx.x, seg = threadIdx.y;
+  const int xb = (v.rx0 & ~1) + blockIdx.x * (2 * kLanes);
+  if (xb > v.rx1) return;  // whole block outside this view's ROI
+  const int x = xb + 2 * lane;  // columns x, x + 1
+  const bool pair_ok = x <= v.rx1;
+  const unsigned valid = ((x >= v.rx0 && x <= v.rx1) ? 0x0000FFFFu : 0u) |
+                         ((x + 1 >= v.rx0 && x + 1 <= v.rx1) ? 0xFFFF0000u : 0u);
+  const int roi_h = v.ry1 - v.ry0 + 1;
+  const int seglen = (roi_h + kSegs - 1) / kSegs;
+  const int ys = v.ry0 + seg * seglen;
+  const int rows = max(0, min(seglen, v.ry1 + 1 - ys));
+  const int pitch2 = sdf_pitch(v.width) / 2;  // row pitch in 32-bit words
+  const unsigned* __restrict__ rowd =
+      reinterpret_cast<const unsigned*>(view_rowd(v)) + (size_t)ys * pitch2 + (x >> 1);
+  unsigned* __restrict__ cold =
+      reinterpret_cast<unsigned*>(view_cold(v)) + (size_t)ys * pitch2 + (x >> 1);
+
+  extern __shared__ unsigned s_strip[];  // [segment][row][lane]; segments padded apart by 16 banks
+  unsigned* mine = s_strip + (size_t)seg * (seglen_max * kLanes + 16) + lane;
+  __shared__ unsigned s_fa[kSegs][kLanes + 1], s_fb[kSegs][kLanes + 1], s_ba[kSegs][kLanes + 1],
+      s_bb[kSegs][kLanes + 1];
+
+  unsigned fa = kPackInf2, fb = kPackInf2, bla = kPackInf2, blb = kPackInf2;
+  if (pair_ok) {
+    unsigned iv = 0;  // (i, i)
+#pragma unroll 8
+    for (int i = 0; i < rows; i++) {
+      const unsigned r = __ldg(rowd + (size_t)i * pitch2);
+      const unsigned ga = __vmaxs2(__vneg2(r), 0u);  // seeds: 0 on the other class, row distance else
+      const unsigned gb = __vmaxs2(r, 0u);
+      fa = __viaddmin_s16x2(fa, kPackOne2, ga);
+      fb = __viaddmin_s16x2(fb, kPackOne2, gb);
+      bla = __viaddmin_s16x2(fa, iv, bla);
+      blb = __viaddmin_s16x2(fb, iv, blb);
+      iv = __vadd2(iv, kPackOne2);
+      mine[i * kLanes] = __vsub2(fb, fa);
+    }
+  }
+  s_fa[seg][lane] = fa;
+  s_fb[seg][lane] = fb;
+  __syncthreads();
+  unsigned cfa = kPackInf2, cfb = kPackInf2;
+  for (int s = 0; s < seg; s++) {
+    const unsigned gap = pack_dup((seg - 1 - s) * seglen);
+    cfa = __vmins2(cfa, __vadd2(s_fa[s][lane], gap));
+    cfb = __vmins2(cfb, __vadd2(s_fb[s][lane], gap));
+  }
+  s_ba[seg][lane] = rows > 0 ? __vmins2(bla, __vadd2(cfa, kPackOne2)) : kPackInf2;
+  s_bb[seg][lane] = rows > 0 ? __vmins2(blb, __vadd2(cfb, kPackOne2)) : kPackInf2;
+  __syncthreads();
+  unsigned da = kPackInf2, db = kPackInf2;
+  for (int s = seg + 1; s < kSegs; s++) {
+    const unsigned gap = pack_dup((s - seg - 1) * seglen);
+    da = __vmins2(da, __vadd2(s_ba[s][lane], gap));
+    db = __vmins2(db, __vadd2(s_bb[s][lane], gap));
+  }
+  unsigned mx = 0;
+  if (pair_ok) {
+    unsigned ca = __vadd2(cfa, pack_dup(rows)), cb = __vadd2(cfb, pack_dup(rows));  // cf + i + 1
+#pragma unroll 8
+    for (int i = rows - 1; i >= 0; i--) {
+      const unsigned f = mine[i * kLanes];  // this thread's own forward result
+      const unsigned fat = __vmins2(__vmaxs2(__vneg2(f), 0u), ca);
+      const unsigned fbt = __vmins2(__vmaxs2(f, 0u), cb);
+      da = __viaddmin_s16x2(da, kPackOne2, fat);
+      db = __viaddmin_s16x2(db, kPackOne2, fbt);
+      ca = __vadd2(ca, kPackMinusOne2);
+      cb = __vadd2(cb, kPackMinusOne2);
+      mx = __vmaxs2(mx, __vmaxs2(da, db));
+      cold[(size_t)i * pitch2] = __vsub2(db, da);
+    }
+  }
+  mx &= valid;
+  int local_max = max((int)(mx & 0xFFFFu), (int)(mx >> 16));
+  if (local_max >= kPackInf) local_max = INT_MAX;
+  local_max = __reduce_max_sync(0xffffffffu, local_max);
+  if ((threadIdx.y * kLanes + threadIdx.x) % 32 == 0 && local_max > 0) atomicMax(v.absmax, local_max);
+}
+
 // ---- pass 2 (Euclidean mode): exact squared distance along the column --------------------------
 // No counterpart in the reference (its transform is the L1 one above); offered because hosts may
 // want the true Euclidean silhouette distance.  D2(x, y) = min over y' of (y - y')^2 + g(x, y')^2
@@ -792,8 +882,31 @@ void launch_sdf2d(const SdfView* views_host, int n_views, int mode, int normaliz
   if (mode == kSdfSignedL2) {
     sdf_col_l2_kernel<<<dim3((max_cols + 127) / 128, n_views), 128, 0, stream>>>(views_dev);
   } else if (max_dist_bound <= 16000) {
-    sdf_col_pack_kernel<<<dim3((max_cols + 1 + 63) / 64, n_views), dim3(32, kPackSegs), 0, stream>>>(
-        views_dev);
+    // forward results on chip when the strip fits one block's shared memory (64 columns, else 32)
+    constexpr size_t kStripBudget = 200 * 1024;
+    const int seglen16 = (max_rows + 15) / 16, seglen32 = (max_rows + 31) / 32;
+    const size_t strip64 = (size_t)16 * (seglen16 * 32 + 16) * sizeof(unsigned);
+    const size_t strip32 = (size_t)32 * (seglen32 * 16 + 16) * sizeof(unsigned);
+    static bool strip_attr[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !strip_attr[dev]) {
+      cudaFuncSetAttribute(sdf_col_pack_smem_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)kStripBudget);
+      cudaFuncSetAttribute(sdf_col_pack_smem_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)kStripBudget);
+      strip_attr[dev] = true;
+    }
+    if (strip64 <= kStripBudget) {
+      sdf_col_pack_smem_kernel<32><<<dim3((max_cols + 1 + 63) / 64, n_views), dim3(32, 16), strip64,
+                                     stream>>>(views_dev, seglen16);
+    } else if (strip32 <= kStripBudget) {
+      sdf_col_pack_smem_kernel<16><<<dim3((max_cols + 1 + 31) / 32, n_views), dim3(16, 32), strip32,
+                                     stream>>>(views_dev, seglen32);
+    } else {
+      sdf_col_pack_kernel<<<dim3((max_cols + 1 + 63) / 64, n_views), dim3(32, kPackSegs), 0,
+                            stream>>>(views_dev);
+    }
   } else if (max_seglen <= kColMaxSegLen) {
     const size_t smem = (size_t)32 * 32 * max_seglen * sizeof(int16_t);
     static bool attr_set[64] = {false};
