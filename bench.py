@@ -378,12 +378,16 @@ def run_ours(args, cfg):
     # ncu's FMA-pipe utilisation measures, and it is `frac`; the algorithmic one is kept beside it.
     sass_s = 38.0 if cfg["weighted"] else 35.0
     sass_1 = sass_s - 9.0
-    pipe_achieved = (pairs_s * sass_s + pairs_1 * sass_1) * vpt / args.steps / \
+    # warps leave the view loop once the update cap has retired all their voxels: count the view
+    # iterations they really executed (256 voxel-views of instructions each), not the pairs
+    iters = classes["warp_iterations"]
+    pipe_achieved = (iters["sampling"] * sass_s + iters["all_ones"] * sass_1) * 256.0 / args.steps / \
         (fus_ms / args.steps * 1e-3) / 1e12
     roofline = {"kernel": "fuse_kernel", "bound": "fp32_issue", "achieved": pipe_achieved,
                 "peak": fp32_peak, "unit": "T lane-ops/s", "frac": pipe_achieved / fp32_peak,
-                "achieved_is": "FP32 lane-operations the kernel issues (static SASS count per tile "
-                               "class x executed voxel-views) / fusion time",
+                "achieved_is": "FP32 lane-operations the kernel issues (static SASS count per path x "
+                               "view iterations the warps executed, counted in the kernel) / fusion time",
+                "issued_voxel_views_per_step": (iters["sampling"] + iters["all_ones"]) * 256.0 / args.steps,
                 "algorithmic": {"achieved": fp32_achieved, "frac": fp32_achieved / fp32_peak,
                                 "ops_per_voxel_view": {"sampling": ops_s, "all_ones": ops_1}},
                 "traffic": traffic,

@@ -147,6 +147,18 @@ int vcb_carve_sdfs(vcb_carver* c, int32_t n_views, const vcb_view* views,
 int vcb_carve_sdfs_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
                           const float* const* sdfs_dev);
 
+/* Image1b::Load (image.h:76-101) + Carve for a batch of silhouette FILES: the files are decoded on
+ * host threads (n_threads <= 0: one per hardware thread) into page-locked memory, one fusion launch
+ * worth at a time, and carved as by vcb_carve_masks - decoding the next files overlaps the GPU
+ * work on the previous ones.  Decoded here: 8-bit greyscale non-interlaced PNG (the reference's
+ * data/mask_*.png; same pixels as its stb loader gives) and binary PGM (P5, maxval 255); other
+ * files are refused with VCB_ERR_UNSUPPORTED.  views[i].width / height must be the image's size.
+ * vcb_load_mask_file decodes one file into `pixels` (capacity bytes; NULL: only report the size). */
+int vcb_carve_mask_files(vcb_carver* c, int32_t n_views, const vcb_view* views,
+                         const char* const* paths, int32_t n_threads);
+int vcb_load_mask_file(const char* path, uint8_t* pixels, size_t capacity, int32_t* width,
+                       int32_t* height);
+
 /* Free functions of voxel_carver.h:120-126 on HOST buffers, run on CUDA device `device` (the
  * caller's current device is restored before they return; they allocate and free their device
  * buffers per call - hosts that transform many images should queue them on a carver instead).
@@ -286,8 +298,13 @@ int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev);
  * pairs[] counts, in this order: general path (sampling with per-voxel range tests), all texels
  * 1.0f (load-free path), all texels kVal (view skipped: every sample would fail the truncation test
  * of voxel_carver.cc:478-480), projection strictly inside the ROI (sampling without range tests),
- * projection outside the ROI (skipped, voxel_carver.cc:462-472).  Calling it synchronises. */
-int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile);
+ * projection outside the ROI (skipped, voxel_carver.cc:462-472).  warp_iterations[] (may be NULL):
+ * view iterations the warps really executed on the load-free path [0] and on the sampling paths
+ * [1]; one iteration is 256 voxel-views of instructions (32 threads x 8 voxels).  It is less than
+ * the pair counts suggest once voxel_max_update_num has retired voxels (voxel_carver.cc:447-450):
+ * a warp whose voxels have all reached the cap leaves the view loop.  Calling it synchronises. */
+int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile,
+                            uint64_t warp_iterations[2]);
 
 /* ---- one grid across several GPUs (z slabs) ---------------------------------------------------
  * No counterpart in the reference, which is single-process and single-device: a vcb_sharded stands
@@ -341,6 +358,9 @@ int vcb_sharded_carve_masks(vcb_sharded* s, int32_t n_views, const vcb_view* vie
                             const uint8_t* const* masks, float* const* sdf_out);
 int vcb_sharded_carve_masks_device(vcb_sharded* s, int32_t n_views, const vcb_view* views,
                                    const uint8_t* const* masks_dev, float* const* sdf_out_dev);
+/* vcb_carve_mask_files for the slabs: every process decodes only the files whose masks it uploads. */
+int vcb_sharded_carve_mask_files(vcb_sharded* s, int32_t n_views, const vcb_view* views,
+                                 const char* const* paths, int32_t n_threads);
 /* Carve(camera, roi, sdf) with ready-made HOST float SDF images (voxel_carver.cc:415-496): every
  * slab fuses them as given. */
 int vcb_sharded_carve_sdfs(vcb_sharded* s, int32_t n_views, const vcb_view* views,

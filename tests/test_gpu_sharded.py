@@ -187,4 +187,37 @@ def test_fusion_class_counts(cuda_lib):
     assert sum(c[k] for k in VoxelCarver.TILE_CLASSES) == tiles * 70
     assert c["voxels_per_tile"] == 2048
     assert c["all_ones"] + c["all_kval"] + c["outside"] > 0 and c["inside"] + c["general"] > 0
+    assert c["warp_iterations"]["all_ones"] + c["warp_iterations"]["sampling"] > 0
     assert sum(car.fusion_class_counts()[k] for k in VoxelCarver.TILE_CLASSES) == 0  # cleared
+
+
+def test_carve_mask_files_single_and_slabs(cuda_lib, port, tmp_path):
+    """vcb_carve_mask_files / vcb_sharded_carve_mask_files: silhouettes arriving as PNG and PGM files
+    (decoded on host threads inside the library, 70 files = two batches) must give the grid and the
+    mesh of the same masks handed over as arrays - here checked against the oracle."""
+    from tests.test_ingest_host import write_png
+    o, opt, cams, masks = scene(n=64, views=70, size=160)
+    orc = oracle_carve(port, opt, cams, masks)
+    ws, wn = orc.download()
+    paths = []
+    for i, m in enumerate(masks):
+        if i % 5 == 4:
+            p = tmp_path / ("m%03d.pgm" % i)
+            with open(p, "wb") as f:
+                f.write(b"P5\n160 160\n255\n" + m.tobytes())
+        else:
+            p = tmp_path / ("m%03d.png" % i)
+            write_png(p, m, filters=(i % 5,), level=1 + i % 9)
+        paths.append(p)
+    one = VoxelCarver(o)
+    assert one.Init() and one.carve_files(cams, paths, (160, 160))
+    gs, gn = one.download_grid()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    eng = sharded.LocalSlabs(o, 3)
+    assert eng.carve_files(cams, paths, (160, 160), n_threads=3)
+    gs, gn = eng.download_grid()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(eng.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)
+    # a file whose size differs from what the view says is refused
+    with pytest.raises(Exception, match="the view says"):
+        one.carve_files(cams[:1], paths[:1], (128, 128))

@@ -10,4 +10,4 @@ from .capi import LibraryMissing, VcbError, load_library  # noqa: F401
 from .carver import (Camera, OrthoCamera, PinholeCamera, SdfInterpolation, SdfMetric,  # noqa: F401
                      UpdateOutsideImage, VoxelCarver, VoxelCarverOption, VoxelUpdate,
                      VoxelUpdateOption, distance_transform_l1, make_signed_distance_field,
-                     signed_distance_to_color, w2c_from_c2w)
+                     load_mask_file, signed_distance_to_color, w2c_from_c2w)

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvacancy_b200.so")
 SOURCES = ["carver.cu", "sdf2d.cu", "fusion.cu", "extract_voxel.cu", "marching_cubes.cu", "ply.cu",
-           "sharded.cu", "checkpoint.cu"]
+           "sharded.cu", "checkpoint.cu", "ingest.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # never contract a*b+c: the fused grid must match the reference's one-rounding-per-op arithmetic

@@ -50,7 +50,8 @@ EXPORTS = [
     "vcb_extract_voxel_count", "vcb_extract_voxel_fill", "vcb_extract_voxel_occupancy",
     "vcb_download_grid", "vcb_upload_grid", "vcb_grid_device", "vcb_stage_times",
     "vcb_fusion_class_counts", "vcb_save_grid", "vcb_load_grid", "vcb_sharded_save_grid",
-    "vcb_sharded_load_grid",
+    "vcb_sharded_load_grid", "vcb_carve_mask_files", "vcb_load_mask_file",
+    "vcb_sharded_carve_mask_files",
     "vcb_ply_header", "vcb_ply_body_size", "vcb_ply_body_fill", "vcb_ply_format",
     "vcb_sharded_create", "vcb_sharded_unique_id", "vcb_sharded_create_rank", "vcb_sharded_destroy",
     "vcb_sharded_last_error", "vcb_sharded_info", "vcb_sharded_bounds", "vcb_sharded_repartition",
@@ -124,7 +125,11 @@ def load_library(path=LIB_PATH):
     L.vcb_upload_grid.argtypes = [vp, fp, ip]
     L.vcb_grid_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     L.vcb_stage_times.argtypes = [vp, fp, C.POINTER(i64)]
-    L.vcb_fusion_class_counts.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(i64)]
+    L.vcb_fusion_class_counts.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(i64),
+                                          C.POINTER(C.c_uint64)]
+    L.vcb_carve_mask_files.argtypes = [vp, i32, C.POINTER(View), C.POINTER(C.c_char_p), i32]
+    L.vcb_sharded_carve_mask_files.argtypes = [vp, i32, C.POINTER(View), C.POINTER(C.c_char_p), i32]
+    L.vcb_load_mask_file.argtypes = [C.c_char_p, vp, C.c_size_t, ip, ip]
     L.vcb_save_grid.argtypes = [vp, C.c_char_p]
     L.vcb_load_grid.argtypes = [vp, C.c_char_p, ip]
     L.vcb_sharded_save_grid.argtypes = [vp, C.c_char_p]

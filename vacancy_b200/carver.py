@@ -297,6 +297,15 @@ class VoxelCarver:
         self._check(self._lib.vcb_carve_sdfs(self._h, n, views, _ptr_array(imgs)))
         return True
 
+    def carve_files(self, cameras, paths, size, n_threads=0):
+        """Image1b::Load + Carve for silhouette files (8-bit grey PNG / binary PGM) of `size` =
+        (width, height): decoded on host threads inside the library (vcb_carve_mask_files)."""
+        n = len(paths)
+        views = (capi.View * n)(*[make_view(c, size[0], size[1]) for c in cameras])
+        arr = (C.c_char_p * n)(*[str(p).encode() for p in paths])
+        self._check(self._lib.vcb_carve_mask_files(self._h, n, views, arr, int(n_threads)))
+        return True
+
     def carve_device(self, views, device_ptrs, masks=True):
         """Stream-ordered fusion of images already resident on the carver's GPU (ints = device
         pointers, e.g. torch tensor.data_ptr())."""
@@ -416,10 +425,13 @@ class VoxelCarver:
         """How the fusion kernel treated the (voxel tile, view) pairs since the last call:
         {class: pairs} plus "voxels_per_tile" (see vcb_fusion_class_counts)."""
         pairs = (C.c_uint64 * 5)()
+        iters = (C.c_uint64 * 2)()
         vpt = C.c_int64()
-        self._check(self._lib.vcb_fusion_class_counts(self._h, pairs, C.byref(vpt)))
+        self._check(self._lib.vcb_fusion_class_counts(self._h, pairs, C.byref(vpt), iters))
         out = {k: int(pairs[i]) for i, k in enumerate(self.TILE_CLASSES)}
         out["voxels_per_tile"] = vpt.value
+        # view iterations the warps executed (256 voxel-views each): load-free path, sampling paths
+        out["warp_iterations"] = {"all_ones": int(iters[0]), "sampling": int(iters[1])}
         return out
 
     def save_grid(self, path):
@@ -469,6 +481,17 @@ def make_signed_distance_field(mask, roi_min=None, roi_max=None, minmax_normaliz
         device, mask.ctypes.data_as(C.POINTER(C.c_uint8)), w, h, rmin, rmax,
         int(minmax_normalize), int(use_truncation), C.c_float(truncation_band),
         out.ctypes.data_as(C.POINTER(C.c_float))))
+    return out
+
+
+def load_mask_file(path):
+    """One silhouette file -> uint8 [H, W] (vcb_load_mask_file; the decoder of carve_files)."""
+    L = capi.load_library()
+    w, h = C.c_int32(), C.c_int32()
+    capi.check(L, None, L.vcb_load_mask_file(str(path).encode(), None, 0, C.byref(w), C.byref(h)))
+    out = np.empty((h.value, w.value), np.uint8)
+    capi.check(L, None, L.vcb_load_mask_file(str(path).encode(), C.c_void_p(out.ctypes.data),
+                                             out.size, C.byref(w), C.byref(h)))
     return out
 
 

@@ -531,8 +531,8 @@ int vcb_create(const vcb_options* opt, vcb_carver** out) {
     CREATE_TRY(cudaMemcpy(*dpos[a], c->h_pos[a].data(), dims[a] * sizeof(float), cudaMemcpyHostToDevice));
   }
   CREATE_TRY(c->max_sdf.reserve(sizeof(float) * kMaxViewsPerLaunch));
-  CREATE_TRY(c->cls_counts.reserve(5 * sizeof(unsigned long long)));
-  CREATE_TRY(cudaMemset(c->cls_counts.ptr, 0, 5 * sizeof(unsigned long long)));
+  CREATE_TRY(c->cls_counts.reserve(8 * sizeof(unsigned long long)));
+  CREATE_TRY(cudaMemset(c->cls_counts.ptr, 0, 8 * sizeof(unsigned long long)));
   // sdf = kVal, update_num = 0 (voxel_carver.cc:342, voxel_carver.h:67-68)
   launch_grid_reset(c);
   CREATE_TRY(cudaGetLastError());
@@ -590,6 +590,7 @@ void vcb_destroy(vcb_carver* c) {
                     &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo,
                     &c->iso.segwid, &c->iso.vb};
   for (Scratch* s : all) s->release();
+  c->ingest_pin.release();
   delete c;
 }
 
@@ -1087,11 +1088,12 @@ int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev) {
   return VCB_OK;
 }
 
-int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile) {
+int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile,
+                            uint64_t warp_iterations[2]) {
   if (!c || !pairs) return fail(c, VCB_ERR_INVALID, "null argument");
   int rc = use_device(c, c->opt.device);
   if (rc != VCB_OK) return rc;
-  unsigned long long h[5];
+  unsigned long long h[8];
   CU(c, cudaMemcpyAsync(h, c->cls_counts.ptr, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
   CU(c, cudaMemsetAsync(c->cls_counts.ptr, 0, sizeof(h), c->stream));
   CU(c, cudaStreamSynchronize(c->stream));
@@ -1099,6 +1101,10 @@ int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_pe
   pairs[0] += c->unclassified_pairs;
   c->unclassified_pairs = 0;
   if (voxels_per_tile) *voxels_per_tile = 32 * 8 * 8;
+  if (warp_iterations) {
+    warp_iterations[0] = h[5];
+    warp_iterations[1] = h[6];
+  }
   return VCB_OK;
 }
 

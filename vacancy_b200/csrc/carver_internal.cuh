@@ -62,6 +62,7 @@ struct vcb_carver {
 
   vcb::VoxelExtract vox;
   vcb::IsoExtract iso;
+  vcb::PinnedBuffer ingest_pin;  // decoded mask files on their way to the GPU (vcb_carve_mask_files)
 
   bool timing = true;
   std::vector<vcb::TimedSpan> spans;
@@ -88,6 +89,9 @@ int use_device(vcb_carver* c, int device);
 int validate(const vcb_options* o, int dims[3]);  // voxel_carver.cc:375-389 and :276-301
 int check_view(vcb_carver* c, const vcb_view& v);
 int flush_pending(vcb_carver* c);                 // launches the fusion of the queued views
+// mask files -> pixels on host threads (ingest.cu); wanted == nullptr decodes all n
+int decode_mask_batch(const char* const* paths, const vcb_view* views, int n, const bool* wanted,
+                      uint8_t* out, size_t stride, int n_threads, std::string* err);
 
 // Fuses n <= kMaxViewsPerLaunch views whose float SDF images, 8x8-block flags (may be NULL) and
 // image maxima are already on this carver's device, in one launch on the carver's stream (earlier

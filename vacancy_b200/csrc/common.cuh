@@ -75,8 +75,9 @@ struct FuseParams {
   const float4* view_tab;
   const float4* mz_tab;
   const unsigned char* tile_class;  // [fusion block][view], nullptr = every tile is "mixed"
-  // running totals of (tile, view) pairs per TileClass over all launches (device, 5 counters;
-  // read and cleared by vcb_fusion_class_counts) - what the tile classification actually skipped
+  // running totals over all launches (device, 8 counters; read and cleared by
+  // vcb_fusion_class_counts): [0..4] (tile, view) pairs per TileClass - what the classification
+  // skipped; [5], [6] view iterations the warps executed on the all-ones / the sampling paths
   unsigned long long* class_counts;
   FuseView views[kMaxViewsPerLaunch];
 };
@@ -137,6 +138,13 @@ struct DeviceGuard {
 };
 
 struct Scratch {  // grow-only device buffer
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  cudaError_t reserve(size_t n);
+  void release();
+};
+
+struct PinnedBuffer {  // grow-only page-locked host buffer (ingest.cu)
   void* ptr = nullptr;
   size_t bytes = 0;
   cudaError_t reserve(size_t n);

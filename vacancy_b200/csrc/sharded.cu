@@ -32,6 +32,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <thread>
 
@@ -46,6 +47,7 @@ struct NcclApi {
   void* handle = nullptr;
   ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommInitRankConfig)(ncclComm_t*, int, ncclUniqueId, int, ncclConfig_t*) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t,
                             cudaStream_t) = nullptr;
@@ -87,6 +89,8 @@ bool nccl_load() {
   VCB_SYM(GroupEnd, "ncclGroupEnd")
   VCB_SYM(GetErrorString, "ncclGetErrorString")
 #undef VCB_SYM
+  g_nccl.CommInitRankConfig =
+      reinterpret_cast<decltype(g_nccl.CommInitRankConfig)>(dlsym(h, "ncclCommInitRankConfig"));
   g_nccl.handle = h;
   return true;
 }
@@ -130,6 +134,7 @@ struct vcb_sharded {
   int iso_phase = 0;             // 0 nothing, 1 mesh on the devices
   int64_t total_vox = -1;
   std::vector<int64_t> vox_counts;
+  PinnedBuffer ingest_pin;       // decoded mask files (vcb_sharded_carve_mask_files)
 };
 
 namespace {
@@ -680,7 +685,19 @@ int vcb_sharded_create_rank(const vcb_options* opt, int32_t device, int32_t rank
     ncclUniqueId id;
     memcpy(&id, id128, sizeof(id));
     cudaSetDevice(device);
-    ncclResult_t r = g_nccl.CommInitRank(&s->local[0].comm, world, id, rank);
+    // The gathers run under the fusion kernel, which wants every SM: a few NCCL blocks are enough
+    // to move one chunk (1 GiB at 2048^2) in the time a fusion launch takes.
+    ncclResult_t r;
+    const char* ctas = getenv("VACANCY_B200_NCCL_CTAS");
+    const int max_ctas = ctas ? atoi(ctas) : 8;
+    if (g_nccl.CommInitRankConfig && max_ctas > 0) {
+      ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+      cfg.minCTAs = 1;
+      cfg.maxCTAs = max_ctas;
+      r = g_nccl.CommInitRankConfig(&s->local[0].comm, world, id, rank, &cfg);
+    } else {
+      r = g_nccl.CommInitRank(&s->local[0].comm, world, id, rank);
+    }
     if (r != ncclSuccess) {
       delete s;
       return sfail(nullptr, VCB_ERR_CUDA, "ncclCommInitRank: %s", g_nccl.GetErrorString(r));
@@ -694,6 +711,7 @@ void vcb_sharded_destroy(vcb_sharded* s) {
   DeviceGuard restore_callers_device;
   destroy_carvers(s);
   for (auto& L : s->local) release_rank(L);
+  s->ingest_pin.release();
   delete s;
 }
 
@@ -780,6 +798,41 @@ int vcb_sharded_carve_sdfs(vcb_sharded* s, int32_t n_views, const vcb_view* view
   int rc = flush_chunk(s);
   if (rc != VCB_OK) return rc;
   for (auto& L : s->local) SCAR(s, L, vcb_carve_sdfs(L.car, n_views, views, sdfs));
+  return VCB_OK;
+}
+
+int vcb_sharded_carve_mask_files(vcb_sharded* s, int32_t n_views, const vcb_view* views,
+                                 const char* const* paths, int32_t n_threads) {
+  if (!s) return sfail(nullptr, VCB_ERR_INVALID, "null handle");
+  if (n_views < 0 || (n_views > 0 && (!views || !paths))) return sfail(s, VCB_ERR_INVALID, "null argument");
+  DeviceGuard restore_callers_device;
+  size_t stride = 0;
+  for (int i = 0; i < n_views; i++) {
+    int rc = check_view(nullptr, views[i]);
+    if (rc != VCB_OK) return sfail(s, rc, "%s", vcb_last_error(nullptr));
+    if (!paths[i]) return sfail(s, VCB_ERR_INVALID, "path %d is null", i);
+    if ((rc = ensure_buffers(s, views[i].width, views[i].height)) != VCB_OK) return rc;
+    stride = std::max(stride, align256((size_t)views[i].width * views[i].height));
+  }
+  // One chunk of files at a time, starting on a chunk boundary, so that view i of the batch is
+  // owned by rank i mod world: this process decodes only the files whose masks it will upload.
+  const int batch = s->chunk_cap;
+  SCU(s, s->ingest_pin.reserve(stride * (size_t)std::min(batch, std::max(n_views, 1))));
+  uint8_t* pin = static_cast<uint8_t*>(s->ingest_pin.ptr);
+  for (int first = 0; first < n_views; first += batch) {
+    const int nb = std::min(batch, n_views - first);
+    int rc = flush_chunk(s);
+    if (rc != VCB_OK) return rc;
+    std::vector<char> mine(nb);
+    for (int i = 0; i < nb; i++) mine[i] = local_of(s, i % s->world) != nullptr;
+    std::string err;
+    rc = decode_mask_batch(paths + first, views + first, nb, reinterpret_cast<const bool*>(mine.data()),
+                           pin, stride, n_threads, &err);
+    if (rc != VCB_OK) return sfail(s, rc, "%s", err.c_str());
+    std::vector<const uint8_t*> masks(nb);
+    for (int i = 0; i < nb; i++) masks[i] = pin + (size_t)i * stride;  // read only where mine[i]
+    if ((rc = carve_impl(s, nb, views + first, masks.data(), nullptr, false)) != VCB_OK) return rc;
+  }
   return VCB_OK;
 }
 

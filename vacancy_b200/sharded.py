@@ -173,6 +173,15 @@ class _Engine:
               else self._lib.vcb_sharded_carve_masks)
         self._check(fn(self._h, n, arr, ptrs, None))
 
+    def carve_files(self, cameras, paths, size, n_threads=0):
+        """Silhouette FILES of `size` = (width, height) (vcb_sharded_carve_mask_files): every
+        process decodes only the files whose masks it uploads."""
+        n = len(paths)
+        views = (capi.View * n)(*[make_view(c, size[0], size[1]) for c in cameras])
+        arr = (C.c_char_p * n)(*[str(p).encode() for p in paths])
+        self._check(self._lib.vcb_sharded_carve_mask_files(self._h, n, views, arr, int(n_threads)))
+        return True
+
     def carve_batch(self, cameras, images):
         imgs = [np.ascontiguousarray(i, np.uint8) for i in images]
         views = [make_view(c, m.shape[1], m.shape[0]) for c, m in zip(cameras, imgs)]
