@@ -302,7 +302,10 @@ int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev);
  * view iterations the warps really executed on the load-free path [0] and on the sampling paths
  * [1]; one iteration is 256 voxel-views of instructions (32 threads x 8 voxels).  It is less than
  * the pair counts suggest once voxel_max_update_num has retired voxels (voxel_carver.cc:447-450):
- * a warp whose voxels have all reached the cap leaves the view loop.  Calling it synchronises. */
+ * a warp whose voxels have all reached the cap leaves the view loop; these two are only counted
+ * while vcb_set_statistics(c, 1) is in force (off by default: counting costs about 1 % of the
+ * fusion kernel's time).  Calling vcb_fusion_class_counts synchronises. */
+int vcb_set_statistics(vcb_carver* c, int32_t enabled);
 int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile,
                             uint64_t warp_iterations[2]);
 
@@ -323,8 +326,11 @@ int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_pe
  *   vcb_sharded_create_rank   one process per GPU (`rank` of `world`): exchanges are NCCL calls on
  *                             a communicator built from the 128-byte id that rank 0 obtains from
  *                             vcb_sharded_unique_id and the launcher hands to every rank.  Every
- *                             rank makes the same calls with the same views (masks may be NULL-free
- *                             copies of the same data; only the owner of a view reads its mask).
+ *                             rank makes the same calls with the same views, vcb_sharded_destroy
+ *                             included (only the owner of a view reads its mask).  The ranks map
+ *                             each other's image pools (CUDA IPC) and gather with the copy engines;
+ *                             NCCL carries the signals, the halo / id planes and the mesh
+ *                             (VACANCY_B200_CE_GATHER=0: NCCL all-gathers instead).
  *                             libnccl.so.2 is loaded on first use, never linked.
  *   z_bounds                  NULL (equal slabs) or world + 1 plane indices from 0 to nz; every slab
  *                             holds at least 2 planes.  vcb_sharded_repartition re-creates the slabs

@@ -180,7 +180,9 @@ def test_fusion_class_counts(cuda_lib):
     """vcb_fusion_class_counts: every (tile, view) pair of every launch lands in exactly one class."""
     o, opt, cams, masks = scene(n=64, views=70, size=256)
     car = VoxelCarver(o)
-    assert car.Init() and car.carve_batch(cams, masks)
+    assert car.Init()
+    car.set_statistics(True)
+    assert car.carve_batch(cams, masks)
     car.synchronize()
     c = car.fusion_class_counts()
     tiles = (64 // 32) * (64 // 8) * (64 // 8)
@@ -220,4 +222,6 @@ def test_carve_mask_files_single_and_slabs(cuda_lib, port, tmp_path):
     H.assert_mesh_equal(eng.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)
     # a file whose size differs from what the view says is refused
     with pytest.raises(Exception, match="the view says"):
+        one.carve_files(cams[:1], paths[:1], (200, 200))
+    with pytest.raises(Exception, match="larger than the buffer"):
         one.carve_files(cams[:1], paths[:1], (128, 128))

@@ -49,7 +49,7 @@ EXPORTS = [
     "vcb_extract_iso_import_bottom", "vcb_extract_iso_faces", "vcb_halo_device",
     "vcb_extract_voxel_count", "vcb_extract_voxel_fill", "vcb_extract_voxel_occupancy",
     "vcb_download_grid", "vcb_upload_grid", "vcb_grid_device", "vcb_stage_times",
-    "vcb_fusion_class_counts", "vcb_save_grid", "vcb_load_grid", "vcb_sharded_save_grid",
+    "vcb_fusion_class_counts", "vcb_set_statistics", "vcb_save_grid", "vcb_load_grid", "vcb_sharded_save_grid",
     "vcb_sharded_load_grid", "vcb_carve_mask_files", "vcb_load_mask_file",
     "vcb_sharded_carve_mask_files",
     "vcb_ply_header", "vcb_ply_body_size", "vcb_ply_body_fill", "vcb_ply_format",
@@ -125,6 +125,7 @@ def load_library(path=LIB_PATH):
     L.vcb_upload_grid.argtypes = [vp, fp, ip]
     L.vcb_grid_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     L.vcb_stage_times.argtypes = [vp, fp, C.POINTER(i64)]
+    L.vcb_set_statistics.argtypes = [vp, i32]
     L.vcb_fusion_class_counts.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(i64),
                                           C.POINTER(C.c_uint64)]
     L.vcb_carve_mask_files.argtypes = [vp, i32, C.POINTER(View), C.POINTER(C.c_char_p), i32]

@@ -421,6 +421,10 @@ class VoxelCarver:
 
     TILE_CLASSES = ("general", "all_ones", "all_kval", "inside", "outside")
 
+    def set_statistics(self, enabled):
+        """Counts the view iterations the fusion warps execute (fusion_class_counts) while on."""
+        self._check(self._lib.vcb_set_statistics(self._h, int(bool(enabled))))
+
     def fusion_class_counts(self):
         """How the fusion kernel treated the (voxel tile, view) pairs since the last call:
         {class: pairs} plus "voxels_per_tile" (see vcb_fusion_class_counts)."""

@@ -1088,6 +1088,12 @@ int vcb_grid_device(vcb_carver* c, float** sdf_dev, int32_t** update_num_dev) {
   return VCB_OK;
 }
 
+int vcb_set_statistics(vcb_carver* c, int32_t enabled) {
+  if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
+  c->fp.count_iterations = enabled ? 1 : 0;
+  return VCB_OK;
+}
+
 int vcb_fusion_class_counts(vcb_carver* c, uint64_t pairs[5], int64_t* voxels_per_tile,
                             uint64_t warp_iterations[2]) {
   if (!c || !pairs) return fail(c, VCB_ERR_INVALID, "null argument");

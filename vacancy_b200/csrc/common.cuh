@@ -79,6 +79,7 @@ struct FuseParams {
   // vcb_fusion_class_counts): [0..4] (tile, view) pairs per TileClass - what the classification
   // skipped; [5], [6] view iterations the warps executed on the all-ones / the sampling paths
   unsigned long long* class_counts;
+  int count_iterations;  // fill [5], [6] (vcb_set_statistics; costs about 1 % of the kernel's time)
   FuseView views[kMaxViewsPerLaunch];
 };
 size_t fusion_table_bytes(int nx, int ny, int nz_slab);

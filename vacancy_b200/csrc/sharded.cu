@@ -105,6 +105,14 @@ struct ShardRank {  // one slab held by this process
   Scratch img[2], tiles[2], maxs[2], stage[2];
   Scratch sdf_scr, absmax;            // 2D SDF scratch for kSdfSubBatch views
   Scratch ids_out, ids_in, cnt, gather;
+  // one process per GPU: the other ranks' pools mapped into this process (CUDA IPC), [array][half]
+  // [rank]; array 0 images, 1 block flags, 2 maxima.  Empty when the gathers go through NCCL.
+  std::vector<void*> peer[3][2];
+  Scratch ipc_buf, signal;
+  // pulls from different ranks go out on several streams so that several copy engines work
+  static constexpr int kPullStreams = 4;
+  cudaStream_t pull[kPullStreams] = {};
+  cudaEvent_t ev_signal = nullptr, ev_pulled[kPullStreams] = {};
   cudaEvent_t ev_staged[2] = {}, ev_sdf[2] = {}, ev_gathered[2] = {}, ev_fused[2] = {}, ev_misc = nullptr;
   bool used[2] = {false, false};
   int64_t nv = 0, nf = 0, voff = 0, foff = 0;  // this slab's part of the last extracted mesh
@@ -135,6 +143,7 @@ struct vcb_sharded {
   int64_t total_vox = -1;
   std::vector<int64_t> vox_counts;
   PinnedBuffer ingest_pin;       // decoded mask files (vcb_sharded_carve_mask_files)
+  bool ce_gather = true;         // one process per GPU: gather with copy engines over IPC mappings
 };
 
 namespace {
@@ -280,12 +289,80 @@ int init_common(vcb_sharded* s) {
       SCU(s, cudaEventCreateWithFlags(&L.ev_fused[h], cudaEventDisableTiming));
     }
     SCU(s, cudaEventCreateWithFlags(&L.ev_misc, cudaEventDisableTiming));
+    SCU(s, cudaEventCreateWithFlags(&L.ev_signal, cudaEventDisableTiming));
+    for (int p = 0; p < ShardRank::kPullStreams; p++) {
+      SCU(s, cudaStreamCreateWithPriority(&L.pull[p], cudaStreamNonBlocking, hi));
+      SCU(s, cudaEventCreateWithFlags(&L.ev_pulled[p], cudaEventDisableTiming));
+    }
   }
   return VCB_OK;
 }
 
 // buffers sized for images of w x h (grow only); flushes and waits before reallocating
 int flush_chunk(vcb_sharded* s);
+
+// ---- one process per GPU: the pools of the other ranks, mapped with CUDA IPC -----------------------
+// NCCL's all-gather kernels take SMs away from the fusion kernel they run beside (measured on 8
+// GPUs: 52-55.7 ms of fusion per rank against 49.5-52.9 ms with NCCL held to 2 blocks, which then
+// cannot move the data in time).  So the bulk of the gather is done by the copy engines: every
+// rank maps the other ranks' pools once (cudaIpcGetMemHandle / cudaIpcOpenMemHandle, the handles
+// travel through one small NCCL all-gather) and pulls the slots it needs with plain device-to-
+// device copies over NVLink.  NCCL stays the signalling plane: a 4-byte all-gather per chunk tells
+// every rank that all ranks have finished writing their slots (and reading the previous chunk).
+int close_peer_maps(vcb_sharded* s) {
+  for (auto& L : s->local) {
+    SCU(s, cudaSetDevice(L.device));
+    for (int a = 0; a < 3; a++) {
+      for (int hf = 0; hf < 2; hf++) {
+        for (size_t r = 0; r < L.peer[a][hf].size(); r++) {
+          if (L.peer[a][hf][r] && (int)r != L.rank) cudaIpcCloseMemHandle(L.peer[a][hf][r]);
+        }
+        L.peer[a][hf].clear();
+      }
+    }
+  }
+  return VCB_OK;
+}
+
+// every rank reaches this point: a 4-byte all-gather on `stream`, then wait for it on the host
+int nccl_barrier(vcb_sharded* s, ShardRank& L, cudaStream_t stream, bool wait) {
+  SCU(s, L.signal.reserve(sizeof(int) * (size_t)s->world));
+  int* d = static_cast<int*>(L.signal.ptr);
+  SNCCL(s, g_nccl.AllGather(d + L.rank, d, sizeof(int), ncclUint8, L.comm, stream));
+  if (wait) SCU(s, cudaStreamSynchronize(stream));
+  return VCB_OK;
+}
+
+int open_peer_maps(vcb_sharded* s) {
+  ShardRank& L = s->local[0];
+  SCU(s, cudaSetDevice(L.device));
+  constexpr size_t kPer = 6 * sizeof(cudaIpcMemHandle_t);
+  SCU(s, L.ipc_buf.reserve(kPer * (size_t)s->world));
+  cudaIpcMemHandle_t mine[6];
+  Scratch* arrays[3] = {L.img, L.tiles, L.maxs};
+  for (int a = 0; a < 3; a++)
+    for (int hf = 0; hf < 2; hf++) SCU(s, cudaIpcGetMemHandle(&mine[a * 2 + hf], arrays[a][hf].ptr));
+  unsigned char* d = static_cast<unsigned char*>(L.ipc_buf.ptr);
+  SCU(s, cudaMemcpyAsync(d + kPer * L.rank, mine, kPer, cudaMemcpyHostToDevice, L.side));
+  SNCCL(s, g_nccl.AllGather(d + kPer * L.rank, d, kPer, ncclUint8, L.comm, L.side));
+  std::vector<cudaIpcMemHandle_t> all(6 * (size_t)s->world);
+  SCU(s, cudaMemcpyAsync(all.data(), d, kPer * s->world, cudaMemcpyDeviceToHost, L.side));
+  SCU(s, cudaStreamSynchronize(L.side));
+  for (int a = 0; a < 3; a++) {
+    for (int hf = 0; hf < 2; hf++) {
+      L.peer[a][hf].assign(s->world, nullptr);
+      for (int r = 0; r < s->world; r++) {
+        if (r == L.rank) {
+          L.peer[a][hf][r] = arrays[a][hf].ptr;
+          continue;
+        }
+        SCU(s, cudaIpcOpenMemHandle(&L.peer[a][hf][r], all[(size_t)r * 6 + a * 2 + hf],
+                                    cudaIpcMemLazyEnablePeerAccess));
+      }
+    }
+  }
+  return VCB_OK;
+}
 
 int ensure_buffers(vcb_sharded* s, int w, int h) {
   const int mode = s->opt.sdf_metric == VCB_METRIC_L2 ? kSdfSignedL2 : kSdfSigned;
@@ -308,6 +385,12 @@ int ensure_buffers(vcb_sharded* s, int w, int h) {
     SCU(s, cudaStreamSynchronize(L.side));
     SCU(s, cudaStreamSynchronize(L.copy));
   }
+  const bool ipc = s->multi_process && s->ce_gather;
+  if (ipc) {
+    // nobody may free a pool that another rank still has mapped: unmap, meet, then re-allocate
+    if ((rc = close_peer_maps(s)) != VCB_OK) return rc;
+    if ((rc = nccl_barrier(s, s->local[0], s->local[0].side, true)) != VCB_OK) return rc;
+  }
   for (auto& L : s->local) {
     SCU(s, cudaSetDevice(L.device));
     for (int hf = 0; hf < 2; hf++) {
@@ -320,6 +403,7 @@ int ensure_buffers(vcb_sharded* s, int w, int h) {
     SCU(s, L.sdf_scr.reserve(s->scr_bytes * kSdfSubBatch));
     SCU(s, L.absmax.reserve(sizeof(int) * kSdfSubBatch));
   }
+  if (ipc && (rc = open_peer_maps(s)) != VCB_OK) return rc;
   return VCB_OK;
 }
 
@@ -377,7 +461,35 @@ int flush_chunk(vcb_sharded* s) {
   }
   // ---- 2. all-gather of the three pools: rank r's slots are [r*J, (r+1)*J) ----
   if (N > 1) {
-    if (s->multi_process) {
+    if (s->multi_process && s->ce_gather) {
+      // signal: every rank has written its slots of this chunk (and has finished pulling the
+      // previous chunk, which sits before this call on its side stream); then pull the other
+      // ranks' slots with the copy engines
+      ShardRank& L = s->local[0];
+      int rc = nccl_barrier(s, L, L.side, false);
+      if (rc != VCB_OK) return rc;
+      const size_t slot[3] = {s->slot_img, s->slot_tiles, sizeof(float)};
+      Scratch* arrays[3] = {L.img, L.tiles, L.maxs};
+      SCU(s, cudaEventRecord(L.ev_signal, L.side));
+      for (int p = 0; p < ShardRank::kPullStreams; p++) SCU(s, cudaStreamWaitEvent(L.pull[p], L.ev_signal, 0));
+      for (int k = 1; k < N; k++) {
+        const int r = (L.rank + k) % N;  // every rank starts with another peer
+        int owned = 0;
+        for (int j = 0; j * N + r < cnt; j++) owned++;
+        if (owned == 0) continue;
+        cudaStream_t ps = L.pull[k % ShardRank::kPullStreams];
+        for (int a = 0; a < 3; a++) {
+          const size_t off = (size_t)r * J * slot[a];
+          SCU(s, cudaMemcpyAsync(static_cast<unsigned char*>(arrays[a][h].ptr) + off,
+                                 static_cast<const unsigned char*>(L.peer[a][h][r]) + off,
+                                 (size_t)owned * slot[a], cudaMemcpyDeviceToDevice, ps));
+        }
+      }
+      for (int p = 0; p < ShardRank::kPullStreams; p++) {
+        SCU(s, cudaEventRecord(L.ev_pulled[p], L.pull[p]));
+        SCU(s, cudaStreamWaitEvent(L.side, L.ev_pulled[p], 0));
+      }
+    } else if (s->multi_process) {
       ShardRank& L = s->local[0];
       SNCCL(s, g_nccl.GroupStart());
       SNCCL(s, g_nccl.AllGather(static_cast<unsigned char*>(L.img[h].ptr) + (size_t)L.rank * J * s->slot_img,
@@ -568,7 +680,7 @@ void release_rank(ShardRank& L) {
   cudaSetDevice(L.device);
   Scratch* all[] = {&L.img[0], &L.img[1], &L.tiles[0], &L.tiles[1], &L.maxs[0], &L.maxs[1],
                     &L.stage[0], &L.stage[1], &L.sdf_scr, &L.absmax, &L.ids_out, &L.ids_in,
-                    &L.cnt, &L.gather};
+                    &L.cnt, &L.gather, &L.ipc_buf, &L.signal};
   for (Scratch* b : all) b->release();
   for (int h = 0; h < 2; h++) {
     if (L.ev_staged[h]) cudaEventDestroy(L.ev_staged[h]);
@@ -577,6 +689,11 @@ void release_rank(ShardRank& L) {
     if (L.ev_fused[h]) cudaEventDestroy(L.ev_fused[h]);
   }
   if (L.ev_misc) cudaEventDestroy(L.ev_misc);
+  if (L.ev_signal) cudaEventDestroy(L.ev_signal);
+  for (int p = 0; p < ShardRank::kPullStreams; p++) {
+    if (L.ev_pulled[p]) cudaEventDestroy(L.ev_pulled[p]);
+    if (L.pull[p]) cudaStreamDestroy(L.pull[p]);
+  }
   if (L.comm) g_nccl.CommDestroy(L.comm);
   if (L.main) cudaStreamDestroy(L.main);
   if (L.side && L.side != L.main) cudaStreamDestroy(L.side);
@@ -674,6 +791,7 @@ int vcb_sharded_create_rank(const vcb_options* opt, int32_t device, int32_t rank
   s->opt = *opt;
   s->world = world;
   s->multi_process = world > 1;
+  s->ce_gather = env_flag("VACANCY_B200_CE_GATHER", true);
   s->local.resize(1);
   s->local[0].rank = rank;
   s->local[0].device = device;
@@ -685,11 +803,11 @@ int vcb_sharded_create_rank(const vcb_options* opt, int32_t device, int32_t rank
     ncclUniqueId id;
     memcpy(&id, id128, sizeof(id));
     cudaSetDevice(device);
-    // The gathers run under the fusion kernel, which wants every SM: a few NCCL blocks are enough
-    // to move one chunk (1 GiB at 2048^2) in the time a fusion launch takes.
+    // VACANCY_B200_NCCL_CTAS caps the blocks NCCL may use (experiments; with the copy-engine gather
+    // NCCL only carries signals and small exchanges).
     ncclResult_t r;
     const char* ctas = getenv("VACANCY_B200_NCCL_CTAS");
-    const int max_ctas = ctas ? atoi(ctas) : 8;
+    const int max_ctas = ctas ? atoi(ctas) : 0;  // 0: NCCL's own choice
     if (g_nccl.CommInitRankConfig && max_ctas > 0) {
       ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
       cfg.minCTAs = 1;
@@ -710,6 +828,12 @@ void vcb_sharded_destroy(vcb_sharded* s) {
   if (!s) return;
   DeviceGuard restore_callers_device;
   destroy_carvers(s);
+  if (s->multi_process && s->ce_gather && !s->local.empty() && !s->local[0].peer[0][0].empty()) {
+    // the ranks unmap each other's pools, meet, and only then free them (every rank destroys its
+    // handle at the same point of the program, like every other call on it)
+    close_peer_maps(s);
+    nccl_barrier(s, s->local[0], s->local[0].side, true);
+  }
   for (auto& L : s->local) release_rank(L);
   s->ingest_pin.release();
   delete s;
