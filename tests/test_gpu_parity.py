@@ -435,6 +435,29 @@ def test_cfg5_slab_with_linear_indices_beyond_2_31(cuda_lib, port):
     assert cnt == wcnt and np.array_equal(flags, wflags)
 
 
+def test_extract_voxel_when_a_touched_voxel_holds_kval(cuda_lib, port):
+    """A caller's own SDF image may contain kVal; fused without truncation (nearest-neighbour
+    sampling, first touch assigns the sample, voxel_carver.cc:482-486) a voxel then holds kVal WITH
+    update_num = 1 - and ExtractVoxel emits it (sdf <= 0, extract_voxel.cc:285).  The shortcut that
+    derives "updated" from sdf != kVal must not be taken for such a grid."""
+    o = S.grid_option(32)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, interp=0)
+    cam = S.circle_cameras(4, 96)[1]
+    sdf = port.make_sdf(S.silhouette(cam, S.DUMBBELL), None, True, False, 0.1)
+    sdf[30:60, 20:70] = port.invalid_sdf()
+    car, orc = make_carver(opt), port.carver(opt)
+    assert car.Carve(cam, sdf)
+    orc.carve_sdf(H.to_oracle_camera(cam), sdf)
+    (gs, gn), (ws, wn) = car.download_grid(), orc.download()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    assert int(((ws == port.invalid_sdf()) & (wn >= 1)).sum()) > 0  # the case in question
+    for inside_empty in (False, True):
+        flags, n = car.occupancy(inside_empty)
+        wflags, wcount = orc.occupancy(inside_empty)
+        assert n == wcount and np.array_equal(flags, wflags), inside_empty
+    H.assert_mesh_equal(car.ExtractIsoSurface(), orc.extract_iso(), o.bb_min, o.bb_max)
+
+
 def test_sdf_color_map(cuda_lib, port, bunny):
     """SignedDistance2Color on the device, byte-exact against the oracle."""
     from vacancy_b200 import signed_distance_to_color

@@ -588,7 +588,8 @@ void vcb_destroy(vcb_carver* c) {
                     &c->iso.ibits, &c->iso.vbits, &c->iso.cbits, &c->iso.abits, &c->iso.segcnt,
                     &c->iso.segbase, &c->iso.active, &c->iso.tmp, &c->iso.hkeys, &c->iso.hvals,
                     &c->iso.verts, &c->iso.faces, &c->iso.counters, &c->iso.cinfo,
-                    &c->iso.segwid, &c->iso.vb};
+                    &c->iso.segwid, &c->iso.vb, &c->iso.slot_cube, &c->iso.slot_pre,
+                    &c->iso.cube_slot};
   for (Scratch* s : all) s->release();
   c->ingest_pin.release();
   delete c;
@@ -603,6 +604,7 @@ int vcb_reset(vcb_carver* c) {
   launch_grid_reset(c);
   c->stage_launches[1] += 1;
   c->un_implied = true;
+  c->kval_touched_possible = false;
   c->iso.n_vertices = c->iso.n_faces = -1;
   c->vox.n_voxels = -1;
   CU(c, cudaGetLastError());
@@ -679,6 +681,7 @@ int vcb_carve_sdfs(vcb_carver* c, int32_t n_views, const vcb_view* views,
     max_pix = max(max_pix, (size_t)views[i].width * views[i].height);
   }
   if (n_views == 0) return VCB_OK;
+  if (!c->opt.use_truncation) c->kval_touched_possible = true;
   if ((rc = ensure_pool(c, max_pix)) != VCB_OK) return rc;
   {
     int mw = 0, mh = 0;
@@ -725,6 +728,7 @@ int vcb_carve_sdfs_device(vcb_carver* c, int32_t n_views, const vcb_view* views,
     if (!sdfs_dev[i]) return fail(c, VCB_ERR_INVALID, "sdf %d is null", i);
   }
   if ((rc = flush_pending(c)) != VCB_OK) return rc;
+  if (n_views > 0 && !c->opt.use_truncation) c->kval_touched_possible = true;
   {
     int mw = 0, mh = 0;
     for (int i = 0; i < n_views; i++) {
@@ -1004,13 +1008,14 @@ int vcb_extract_voxel_count(vcb_carver* c, int32_t inside_empty, int64_t* n_voxe
   if (!c) return fail(nullptr, VCB_ERR_INVALID, "null carver");
   int rc = vcb_flush(c);
   if (rc != VCB_OK) return rc;
-  if (inside_empty && c->z_begin > 0 && !c->un_implied)
+  if (inside_empty && c->z_begin > 0 && (!c->un_implied || c->kval_touched_possible))
     return fail(c, VCB_ERR_UNSUPPORTED,
                 "inside_empty on a z slab needs the uploaded grid to keep update_num < 1 <=> sdf == kVal "
                 "(update_num has no halo plane)");
   {
     Span span(c, 2);
-    cudaError_t e = voxel_extract_count(grid_desc(c), inside_empty, &c->vox, c->stream,
+    cudaError_t e = voxel_extract_count(grid_desc(c), inside_empty,
+                                        c->un_implied && !c->kval_touched_possible, &c->vox, c->stream,
                                         &c->stage_launches[2]);
     if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "ExtractVoxel: %s", cudaGetErrorString(e));
   }

@@ -31,7 +31,10 @@ struct vcb_carver {
   float2* wtab = nullptr;
   int wtab_n = 0;
   int64_t max_count = 0;  // upper bound of update_num over the grid (views fused / uploaded)
-  bool un_implied = true;  // update_num < 1  <=>  sdf == kVal (true unless a grid was uploaded)
+  bool un_implied = true;  // update_num < 1  =>  sdf == kVal (true unless a grid was uploaded)
+  // a caller's own SDF images were fused without truncation: a touched voxel may then hold kVal
+  // itself (voxel_carver.cc:482-486 assigns whatever was sampled), so ExtractVoxel reads update_num
+  bool kval_touched_possible = false;
 
   // queued views
   vcb::FuseParams fp;

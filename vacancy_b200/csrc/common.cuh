@@ -161,8 +161,8 @@ struct VoxelExtract {  // state kept between _count and _fill
   int64_t n_voxels = -1;
   int inside_empty = 0;
 };
-cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, VoxelExtract* st,
-                                cudaStream_t stream, int64_t* launches);
+cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, bool un_implied,
+                                VoxelExtract* st, cudaStream_t stream, int64_t* launches);
 cudaError_t voxel_extract_fill(const GridDesc& g, VoxelExtract* st, float* vertices_host,
                                int32_t* faces_host, cudaStream_t stream, int64_t* launches);
 cudaError_t voxel_extract_flags(const GridDesc& g, VoxelExtract* st, uint8_t* flags_host,
@@ -182,10 +182,11 @@ cudaError_t ply_emit(const float* verts_dev, const int32_t* faces_dev, PlyText* 
 
 struct IsoExtract {
   Scratch ibits, vbits, cbits, abits, segcnt, segbase, active, tmp, hkeys, hvals, verts, faces,
-      counters, cinfo, segwid, vb;
+      counters, cinfo, segwid, vb, slot_cube, slot_pre, cube_slot;
   int64_t n_vertices = -1, n_faces = -1;
   int phase = 0;          // 0 nothing, 1 counted, 2 vertices emitted, 3 faces emitted
-  unsigned n_active = 0;  // active segments
+  unsigned n_active = 0;  // active segments (slots)
+  unsigned n_cubes = 0;   // active cubes
   uint64_t hmask = 0;
   double iso_level = 0.0;
   int linear_interp = 1;

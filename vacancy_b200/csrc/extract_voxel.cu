@@ -159,6 +159,14 @@ __host__ __device__ inline SegGeom seg_geom(const GridDesc& g) {
 // 32 voxels into one bitmap word with a ballot; each row's count is the sum of its popcounts.
 constexpr int kFlagRows = 2;
 
+// kImplied: the grid was carved (never uploaded), so update_num >= 1 exactly where sdf != kVal and
+// update_num need not be read at all - half the traffic of the pass.
+template <bool kImplied>
+__device__ __forceinline__ bool updated(const GridDesc& g, size_t id, float s) {
+  return kImplied ? (s != kInvalidSdf) : (g.update_num[id] >= 1);
+}
+
+template <bool kImplied>
 __device__ __forceinline__ bool emit_predicate(const GridDesc& g, int inside_empty, float s, int n,
                                                size_t id, int x, int y, int zl) {
   if (!inside_empty) return !(s > 0.0f || n < 1);  // extract_voxel.cc:285
@@ -166,10 +174,17 @@ __device__ __forceinline__ bool emit_predicate(const GridDesc& g, int inside_emp
   const size_t plane = (size_t)g.nx * g.ny;
   const bool tiny = fabsf(s) < FLT_MIN;
   bool emit = false;
-  if (x >= 1 && g.update_num[id - 1] >= 1) emit |= (__fmul_rn(s, g.sdf[id - 1]) < 0.0f) || tiny;
-  if (y >= 1 && g.update_num[id - g.nx] >= 1) emit |= (__fmul_rn(s, g.sdf[id - g.nx]) < 0.0f) || tiny;
+  if (x >= 1) {
+    const float o = g.sdf[id - 1];
+    if (updated<kImplied>(g, id - 1, o)) emit |= (__fmul_rn(s, o) < 0.0f) || tiny;
+  }
+  if (y >= 1) {
+    const float o = g.sdf[id - g.nx];
+    if (updated<kImplied>(g, id - g.nx, o)) emit |= (__fmul_rn(s, o) < 0.0f) || tiny;
+  }
   if (zl >= 1) {
-    if (g.update_num[id - plane] >= 1) emit |= (__fmul_rn(s, g.sdf[id - plane]) < 0.0f) || tiny;
+    const float o = g.sdf[id - plane];
+    if (updated<kImplied>(g, id - plane, o)) emit |= (__fmul_rn(s, o) < 0.0f) || tiny;
   } else if (g.z_begin > 0 && g.halo >= 1) {
     // first plane of a z slab: the voxel below lives in the halo plane stored right under the slab
     // (filled from the lower slab before this kernel runs); update_num has no halo, but a grid that
@@ -180,6 +195,7 @@ __device__ __forceinline__ bool emit_predicate(const GridDesc& g, int inside_emp
   return emit;
 }
 
+template <bool kImplied>
 __global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int inside_empty,
                                                          uint32_t* __restrict__ bits,
                                                          uint64_t* __restrict__ rowcnt) {
@@ -206,7 +222,7 @@ __global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int i
         const bool ok = row_ok && x + 32 * q < g.nx;
         const size_t id = (size_t)(row0 + r) * g.nx + x + 32 * q;
         s[r][q] = ok ? g.sdf[id] : 1.0f;
-        n[r][q] = ok ? g.update_num[id] : 0;
+        n[r][q] = !ok ? 0 : (kImplied ? (s[r][q] != kInvalidSdf ? 1 : 0) : g.update_num[id]);
       }
     }
 #pragma unroll
@@ -218,7 +234,7 @@ __global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int i
       for (int q = 0; q < 4; q++) {
         const int xx = x + 32 * q;
         const bool ok = row < n_rows && xx < g.nx;
-        const bool emit = ok && emit_predicate(g, inside_empty, s[r][q], n[r][q],
+        const bool emit = ok && emit_predicate<kImplied>(g, inside_empty, s[r][q], n[r][q],
                                                (size_t)row * g.nx + xx, xx, y, zl);
         const unsigned w_q = __ballot_sync(0xffffffffu, emit);
         if (lane == q) word = w_q;
@@ -303,8 +319,8 @@ __global__ void __launch_bounds__(256) voxel_unpack_kernel(const GridDesc g,
 
 }  // namespace
 
-cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, VoxelExtract* st,
-                                cudaStream_t stream, int64_t* launches) {
+cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, bool un_implied,
+                                VoxelExtract* st, cudaStream_t stream, int64_t* launches) {
   const SegGeom sg = seg_geom(g);
   st->n_voxels = -1;
   st->inside_empty = inside_empty;
@@ -317,8 +333,12 @@ cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, VoxelExtrac
   uint32_t* bits = static_cast<uint32_t*>(st->bits.ptr);
   uint64_t* rowcnt = static_cast<uint64_t*>(st->segbase.ptr);
   uint64_t* rowbase = rowcnt + n_rows;
-  voxel_flag_kernel<<<(unsigned)((n_rows + kFlagRows - 1) / kFlagRows), 256, 0, stream>>>(
-      g, inside_empty, bits, rowcnt);
+  const unsigned flag_blocks = (unsigned)((n_rows + kFlagRows - 1) / kFlagRows);
+  if (un_implied) {
+    voxel_flag_kernel<true><<<flag_blocks, 256, 0, stream>>>(g, inside_empty, bits, rowcnt);
+  } else {
+    voxel_flag_kernel<false><<<flag_blocks, 256, 0, stream>>>(g, inside_empty, bits, rowcnt);
+  }
   if (launches) *launches += 1;
   e = scan_exclusive_u64(rowcnt, rowbase, n_rows, rowbase + n_rows, &st->tmp, stream, launches);
   if (e != cudaSuccess) return e;

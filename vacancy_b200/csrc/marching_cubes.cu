@@ -18,12 +18,16 @@
 //   mc_bits_kernel   dense, HBM-bound: reads each sdf value once (4 B/voxel), writes 2 bits/voxel:
 //                    I = (double)sdf < iso  (:121-128)   V = sdf != kVal (:103-112)
 //   mc_cube_kernel   bitmap-only (1/16 of the data): per S, word-parallel "all 8 corners valid" (C)
-//                    and "8 inside-bits not all equal" -> active-cube word A; compacts active S.
-//   mc_count_kernel  warp per active S: cube index, edge ownership, counts -> per-S (nv, nt).
-//   scan             exclusive prefix over S in raster order (extract_voxel.cu).
-//   mc_vertex_kernel warp per active S: owned vertices -> positions (float64 interpolation, :28-46),
-//                    written at their final index; edge -> vertex id goes into a hash table.
-//   mc_face_kernel   warp per active S: triangles in table order, ids looked up by edge key.
+//                    and "8 inside-bits not all equal" -> active-cube word A; S with A != 0 get a slot
+//                    in the compact lists, every owned S its entry in the dense S -> slot map.
+//   mc_list_kernel   thread per slot: the slot's cubes get consecutive places in the cube list.
+//   mc_count_kernel  thread per ACTIVE CUBE: cube index, edge ownership -> counts per S and per row.
+//   scan             exclusive prefix over the rows in raster order (extract_voxel.cu), then
+//   mc_rowprefix_kernel  warp per row: ids of each slot's first vertex / face.
+//   mc_vertex_kernel thread per active cube: owned vertices -> positions (float64 interpolation,
+//                    :28-46), written at their final index; ids of the vertices the cube is the home
+//                    of stay in cube_ids (the rare others go into a hash table).
+//   mc_face_kernel   thread per active cube: triangles in table order, ids read from the home cubes.
 // Algorithmic bytes: 4 B/voxel + 12 B/vertex + 12 B/face.
 #include <float.h>
 #include <math.h>
@@ -159,20 +163,23 @@ __device__ __forceinline__ unsigned shift_in(unsigned w, unsigned prev) {
   return (w << 1) | (prev >> 31);
 }
 
+// Per stored word: the cube-valid bits; per OWNED segment with at least one active cube (valid, corners
+// not all on one side) a slot in the compact lists - its segment index and its word of active cubes -
+// plus the dense map segment -> slot that the emit passes use to find a neighbour's data.
 __global__ void __launch_bounds__(256)
     mc_cube_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
                    const uint32_t* __restrict__ vbits, const uint32_t* __restrict__ ubits,
-                   uint32_t* __restrict__ cbits, uint32_t* __restrict__ abits,
-                   uint32_t* __restrict__ active, unsigned* __restrict__ n_active,
+                   uint32_t* __restrict__ cbits, uint32_t* __restrict__ slot_seg,
+                   uint32_t* __restrict__ slot_word, unsigned* __restrict__ counters,
                    uint32_t* __restrict__ segwid) {
   const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (w >= m.n_words) return;
+  const bool in_range = w < m.n_words;
   const int sx = (int)(w % m.spr);
   const int64_t row = w / m.spr;
   const int y = (int)(row % m.ny);
   const int z = (int)(row / m.ny) + m.zb;
   unsigned c = 0, a = 0;
-  if (y >= 1 && z >= 1 && z > m.zb) {
+  if (in_range && y >= 1 && z >= 1 && z > m.zb) {
     unsigned all_v = 0xffffffffu, all_i = 0xffffffffu, any_i = 0;
 #pragma unroll
     for (int r = 0; r < 4; r++) {
@@ -187,16 +194,44 @@ __global__ void __launch_bounds__(256)
     if (ubits) c &= ubits[word_index(m, sx, y, z)];  // marching_cubes.cc:88-90
     a = c & any_i & ~all_i;
   }
-  cbits[w] = c;
-  if (z >= m.z_begin) {
+  if (in_range) cbits[w] = c;
+  // Slots are handed out per BLOCK: one 64-bit atomic (slots in the low half, active cubes in the
+  // high half) for all its active segments - one atomic per segment or per warp serialises on the
+  // counter's address (measured: 0.65 ms of this pass at 1024^3).
+  const bool owned = in_range && z >= m.z_begin;
+  if (!owned) a = 0;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned act = __ballot_sync(0xffffffffu, a != 0);
+  const unsigned cubes = __reduce_add_sync(0xffffffffu, (unsigned)__popc(a));
+  __shared__ unsigned s_slots[8], s_cubes[8];
+  __shared__ unsigned s_base;
+  if (lane == 0) {
+    s_slots[warp] = __popc(act);
+    s_cubes[warp] = cubes;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned ns = 0, nc = 0;
+    for (int i = 0; i < 8; i++) {
+      ns += s_slots[i];
+      nc += s_cubes[i];
+    }
+    s_base = ns ? (unsigned)atomicAdd(reinterpret_cast<unsigned long long*>(counters),
+                                      ((unsigned long long)nc << 32) | ns)
+                : 0u;
+  }
+  __syncthreads();
+  unsigned base = s_base;
+  for (unsigned i = 0; i < warp; i++) base += s_slots[i];
+  if (owned) {
     const int64_t seg = seg_index(m, sx, y, z);
-    abits[seg] = a;
     unsigned slot = kNoSlot;
     if (a) {
-      slot = atomicAdd(n_active, 1u);
-      active[slot] = (uint32_t)seg;
+      slot = base + __popc(act & ((1u << lane) - 1u));
+      slot_seg[slot] = (uint32_t)seg;
+      slot_word[slot] = a;
     }
-    segwid[seg] = slot;  // segment -> its place in the active list (the emit passes index by it)
+    segwid[seg] = slot;
   }
 }
 
@@ -206,12 +241,6 @@ struct CubeInfo {
   int ci;          // cube index, marching_cubes.cc:121-128
   unsigned owned;  // crossed edges whose vertex this cube creates
 };
-
-__device__ __forceinline__ unsigned cube_ok(const uint32_t* __restrict__ cbits, const McGeom& m,
-                                            int x, int y, int z) {
-  if (x < 1 || x >= m.nx || y < 1 || y >= m.ny || z < 1 || z <= m.zb) return 0u;
-  return get_bit(cbits, m, x, y, z);
-}
 
 // Configuration and owned edges of the cube of lane `lane` in segment (sx, y, z).  Every lane of
 // the warp reads the same few bitmap words (broadcast loads): the rows (y-1, y) x (z-1, z) of the
@@ -310,29 +339,48 @@ __device__ __forceinline__ int32_t hash_find(const uint64_t* __restrict__ keys,
   }
 }
 
+// ---- compact lists of the sparse passes ---------------------------------------------------------
+// slot  = an owned segment (32 cubes along x) with at least one active cube, in no particular order:
+//         slot_seg[slot], slot_word[slot] (its active cubes), slot_cube[slot] (index of its first cube
+//         in the cube list), slot_cnt[slot] ((vertices << 16) | faces of the segment), slot_pre[slot]
+//         (ids of the segment's first vertex / face);
+// cube  = one active cube; the cubes of a slot are consecutive, in x order: cube_slot[c], cube_info[c]
+//         (configuration | owned edges << 8), cube_ids[c][3] (below).
+// The sparse passes run ONE THREAD PER ACTIVE CUBE: on a surface that crosses a segment once or
+// twice a warp per segment would leave 30 lanes idle.
+//
 // Where a vertex id is kept.  Among the <= 4 cubes sharing a grid edge the first in raster order
 // is the one whose max corner is the edge's upper endpoint - the edge's HOME cube, which sees it as
 // e6 (x-edge), e5 (y-edge) or e10 (z-edge).  When the home cube is non-skipped it owns the vertex;
-// the vertex pass leaves, for every cube of every active segment, the ids of the (up to three)
-// vertices it is the home of: ids3[slot][lane][axis], -1 where it owns none.  Only vertices whose
-// home cube is skipped or does not exist (next to kVal / un-updated voxels, on the grid's low
-// faces, or below this z slab) go through the hash table - in the interior of a carved grid none.
-struct IdTables {
-  const uint32_t* segwid;  // owned segment -> slot in the active list (kNoSlot: no active cube)
-  const int32_t* ids3;     // [slot][lane][axis]
+// the vertex pass leaves, for every active cube, the ids of the (up to three) vertices it is the
+// home of: cube_ids[c][axis], -1 where it owns none.  Only vertices whose home cube is skipped or
+// does not exist (next to kVal / un-updated voxels, on the grid's low faces, or below this z slab)
+// go through the hash table - in the interior of a carved grid none.
+struct McLists {
+  const uint32_t* segwid;     // owned segment -> slot (kNoSlot: no active cube)
+  const uint32_t* slot_seg;
+  const uint32_t* slot_word;
+  const uint32_t* slot_cube;
+  const uint32_t* cube_slot;
+  const uint32_t* cube_info;
+  const int32_t* cube_ids;
   const uint64_t* hkeys;
   const int32_t* hvals;
   uint64_t hmask;
 };
 
 // id of the vertex on the edge with upper endpoint (hx, hy, hz) along `axis` (-1: none)
-__device__ __forceinline__ int32_t vertex_id_of_edge(const McGeom& m, const IdTables& t, int hx,
+__device__ __forceinline__ int32_t vertex_id_of_edge(const McGeom& m, const McLists& t, int hx,
                                                      int hy, int hz, int axis) {
   if (hx >= 1 && hy >= 1 && hz >= m.cz0) {  // a cube of this slab
     const unsigned slot = t.segwid[seg_index(m, hx >> 5, hy, hz)];
     if (slot != kNoSlot) {
-      const int32_t id = t.ids3[((size_t)slot * 32 + (hx & 31)) * 3 + axis];
-      if (id >= 0) return id;
+      const unsigned word = t.slot_word[slot], bit = 1u << (hx & 31);
+      if (word & bit) {
+        const unsigned c = t.slot_cube[slot] + __popc(word & (bit - 1u));
+        const int32_t id = t.cube_ids[(size_t)c * 3 + axis];
+        if (id >= 0) return id;
+      }
     }
   }
   const uint64_t id = ((uint64_t)(hz - (axis == 2)) * m.ny + (hy - (axis == 1))) * m.nx +
@@ -340,61 +388,84 @@ __device__ __forceinline__ int32_t vertex_id_of_edge(const McGeom& m, const IdTa
   return hash_find(t.hkeys, t.hvals, t.hmask, (id << 2) | (uint64_t)axis);
 }
 
-__device__ __forceinline__ void seg_coords(const McGeom& m, int64_t seg, int* sx, int* y, int* z) {
-  *sx = (int)(seg % m.spr);
-  const int64_t row = seg / m.spr;
-  *y = (int)(row % m.ny);
-  *z = (int)(row / m.ny) + m.z_begin;
+// the active cube c: its slot, its position in the slot, its coordinates
+struct CubeAt {
+  unsigned slot, k;
+  int x, y, z;
+  int64_t row;  // owned row (y, z) index
+};
+__device__ __forceinline__ CubeAt cube_at(const McGeom& m, const McLists& t, unsigned c) {
+  CubeAt q;
+  q.slot = t.cube_slot[c];
+  q.k = c - t.slot_cube[q.slot];
+  const int64_t seg = t.slot_seg[q.slot];
+  const int lane = (int)__fns(t.slot_word[q.slot], 0, (int)q.k + 1);  // the k-th active cube
+  q.row = seg / m.spr;
+  q.x = (int)(seg - q.row * m.spr) * 32 + lane;
+  q.y = (int)(q.row % m.ny);
+  q.z = (int)(q.row / m.ny) + m.z_begin;
+  return q;
 }
 
-// (vertex, face) numbers of a segment's first cube: the row's exclusive prefix (scan over rows) plus
-// the counts of the segments before it in the same row, summed by the warp.
-__device__ __forceinline__ void seg_base(const McGeom& m, int64_t seg, int lane,
-                                         const uint32_t* __restrict__ segcnt,
-                                         const uint64_t* __restrict__ rowbase, int64_t* vbase,
-                                         int64_t* fbase) {
-  const int64_t row = seg / m.spr;
-  const int sx = (int)(seg - row * m.spr);
-  unsigned nv = 0, nt = 0;
-  for (int s0 = 0; s0 < sx; s0 += 32) {
-    const int sidx = s0 + lane;
-    const unsigned c = sidx < sx ? segcnt[row * m.spr + sidx] : 0u;
-    nv += c >> 16;
-    nt += c & 0xffffu;
-  }
-  nv = __reduce_add_sync(0xffffffffu, nv);
-  nt = __reduce_add_sync(0xffffffffu, nt);
-  const uint64_t rb = rowbase[row];
-  *vbase = (int64_t)(rb >> 32) + nv;
-  *fbase = (int64_t)(rb & 0xffffffffull) + nt;
+// One thread per slot: where the slot's cubes sit in the cube list.
+__global__ void __launch_bounds__(256)
+    mc_list_kernel(unsigned n_slots, const uint32_t* __restrict__ slot_word,
+                   unsigned* __restrict__ counters, uint32_t* __restrict__ slot_cube,
+                   uint32_t* __restrict__ slot_cnt, uint32_t* __restrict__ cube_slot) {
+  const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= n_slots) return;
+  const int n = __popc(slot_word[slot]);
+  const unsigned base = atomicAdd(counters + 2, (unsigned)n);
+  slot_cube[slot] = base;
+  slot_cnt[slot] = 0;
+  for (int k = 0; k < n; k++) cube_slot[base + k] = slot;
 }
 
-__global__ void __launch_bounds__(128)
-    mc_count_kernel(const McGeom m, const uint32_t* __restrict__ ibits,
-                    const uint32_t* __restrict__ cbits, const uint32_t* __restrict__ abits,
-                    const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
-                    uint32_t* __restrict__ segcnt, unsigned long long* __restrict__ rowcnt,
-                    uint32_t* __restrict__ cinfo) {
+// One thread per active cube: configuration and owned edges; counts per segment and per row.
+__global__ void __launch_bounds__(256)
+    mc_count_kernel(const McGeom m, const McLists t, unsigned n_cubes,
+                    const uint32_t* __restrict__ ibits, const uint32_t* __restrict__ cbits,
+                    uint32_t* __restrict__ cube_info_out, uint32_t* __restrict__ slot_cnt,
+                    unsigned long long* __restrict__ rowcnt) {
+  const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cubes) return;
+  const CubeAt q = cube_at(m, t, c);
+  const CubeInfo info = cube_info(m, ibits, cbits, q.x >> 5, q.y, q.z, q.x & 31);
+  const unsigned nv = __popc(info.owned), nt = d_ntri[info.ci];
+  cube_info_out[c] = (unsigned)info.ci | (info.owned << 8);
+  // per segment: (vertices << 16) | faces (<= 384 and <= 160); per row of segments: 64-bit sums
+  atomicAdd(slot_cnt + q.slot, (nv << 16) | nt);
+  atomicAdd(rowcnt + q.row, ((unsigned long long)nv << 32) | nt);
+}
+
+// One warp per owned row with any active cube: ids of each segment's first vertex / face = the row's
+// exclusive prefix (scan over rows) + the counts of the segments before it in the row.
+__global__ void __launch_bounds__(256)
+    mc_rowprefix_kernel(const McGeom m, int64_t n_rows, const uint32_t* __restrict__ segwid,
+                        const uint32_t* __restrict__ slot_cnt,
+                        const unsigned long long* __restrict__ rowcnt,
+                        const uint64_t* __restrict__ rowbase, uint2* __restrict__ slot_pre) {
   const int lane = threadIdx.x & 31;
-  const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (wid >= *n_active) return;
-  const int64_t seg = active[wid];
-  int sx, y, z;
-  seg_coords(m, seg, &sx, &y, &z);
-  unsigned nv = 0, nt = 0, packed = 0;
-  if ((abits[seg] >> lane) & 1u) {
-    const CubeInfo info = cube_info(m, ibits, cbits, sx, y, z, lane);
-    nv = __popc(info.owned);
-    nt = d_ntri[info.ci];
-    packed = (unsigned)info.ci | (info.owned << 8) | 0x80000000u;
-  }
-  cinfo[(size_t)wid * 32 + lane] = packed;  // cube index + owned-edge mask, reused by the emit passes
-  nv = __reduce_add_sync(0xffffffffu, nv);
-  nt = __reduce_add_sync(0xffffffffu, nt);
-  if (lane == 0) {
-    // per segment: (vertices << 16) | faces (<= 384 and <= 160); per row of segments: 64-bit sums
-    segcnt[seg] = (nv << 16) | nt;
-    atomicAdd(rowcnt + seg / m.spr, ((unsigned long long)nv << 32) | nt);
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= n_rows || rowcnt[row] == 0) return;
+  const uint64_t rb = rowbase[row];
+  unsigned run_v = (unsigned)(rb >> 32), run_f = (unsigned)(rb & 0xffffffffull);
+  for (int s0 = 0; s0 < m.spr; s0 += 32) {
+    const int sx = s0 + lane;
+    const unsigned slot = sx < m.spr ? segwid[row * m.spr + sx] : kNoSlot;
+    const unsigned cnt = slot != kNoSlot ? slot_cnt[slot] : 0u;
+    unsigned iv = cnt >> 16, it = cnt & 0xffffu;
+    const unsigned nv = iv, nt = it;
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned a = __shfl_up_sync(0xffffffffu, iv, o), b = __shfl_up_sync(0xffffffffu, it, o);
+      if (lane >= o) {
+        iv += a;
+        it += b;
+      }
+    }
+    if (slot != kNoSlot) slot_pre[slot] = make_uint2(run_v + iv - nv, run_f + it - nt);
+    run_v += __shfl_sync(0xffffffffu, iv, 31);
+    run_f += __shfl_sync(0xffffffffu, it, 31);
   }
 }
 
@@ -421,43 +492,33 @@ __device__ __forceinline__ void vertex_interp(double iso, const float p1[3], con
   }
 }
 
+// One thread per active cube: the vertices it owns, at their final index, in the order the triangle
+// walk first references their edges.
 __global__ void __launch_bounds__(128)
-    mc_vertex_kernel(const McGeom m, const GridDesc g, const uint32_t* __restrict__ ibits,
-                     const uint32_t* __restrict__ cbits, const uint32_t* __restrict__ abits,
-                     const uint32_t* __restrict__ active, const unsigned* __restrict__ n_active,
-                     const uint32_t* __restrict__ segcnt, const uint64_t* __restrict__ rowbase,
-                     const uint32_t* __restrict__ cinfo, double iso, int linear_interp,
+    mc_vertex_kernel(const McGeom m, const GridDesc g, const McLists t, unsigned n_cubes,
+                     const uint2* __restrict__ slot_pre, double iso, int linear_interp,
                      int64_t vertex_offset, float* __restrict__ vertices,
-                     int32_t* __restrict__ ids3, uint64_t* hkeys, int32_t* hvals, uint64_t hmask) {
-  const int lane = threadIdx.x & 31;
-  const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (wid >= *n_active) return;
-  const int64_t seg = active[wid];
-  int sx, y, z;
-  seg_coords(m, seg, &sx, &y, &z);
-  const int x = sx * 32 + lane;
-  const unsigned packed = cinfo[(size_t)wid * 32 + lane];
-  CubeInfo info;
-  info.ci = (int)(packed & 0xffu);
-  info.owned = (packed >> 8) & 0xfffu;
-  const unsigned nv = __popc(info.owned);
-  unsigned inc = nv;
-  for (int o = 1; o < 32; o <<= 1) {
-    const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += t;
-  }
-  int64_t vbase, fbase;
-  seg_base(m, seg, lane, segcnt, rowbase, &vbase, &fbase);
+                     int32_t* __restrict__ cube_ids, uint64_t* hkeys, int32_t* hvals,
+                     uint64_t hmask) {
+  const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cubes) return;
+  const CubeAt q = cube_at(m, t, c);
+  const unsigned packed = t.cube_info[c];
+  const int ci = (int)(packed & 0xffu);
+  const unsigned owned = (packed >> 8) & 0xfffu;
+  // first vertex of this cube: the segment's first + what the segment's earlier cubes own
+  int64_t vid = slot_pre[q.slot].x;
+  for (unsigned k = 0; k < q.k; k++) vid += __popc((t.cube_info[c - q.k + k] >> 8) & 0xfffu);
   // ids of the vertices on the three edges that end in this cube's max corner (e6 along x, e5 along
-  // y, e10 along z) - the edges this cube is the HOME of; -1 where it owns none (see IdTables)
+  // y, e10 along z) - the edges this cube is the HOME of; -1 where it owns none (see McLists)
   int32_t home_id[3] = {-1, -1, -1};
-  int64_t vid = vbase + (inc - nv);
+  const int x = q.x, y = q.y, z = q.z;
   const size_t plane = (size_t)m.nx * m.ny;
-  const uint64_t ord = nv ? d_order[info.ci] : ~0ull;
+  const uint64_t ord = owned ? d_order[ci] : ~0ull;
   for (int k = 0; k < 12; k++) {
     const int e = (int)((ord >> (4 * k)) & 0xF);
     if (e == 0xF) break;
-    if (!((info.owned >> e) & 1u)) continue;
+    if (!((owned >> e) & 1u)) continue;
     // the two end points of the edge, loaded on demand (most cubes own one or two vertices)
     const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
     const int ax = x + c_corner[a][0], ay = y + c_corner[a][1], az = z + c_corner[a][2];
@@ -488,37 +549,24 @@ __global__ void __launch_bounds__(128)
     }
     vid++;
   }
-  int32_t* __restrict__ out = ids3 + ((size_t)wid * 32 + lane) * 3;
+  int32_t* __restrict__ out = cube_ids + (size_t)c * 3;
   out[0] = home_id[0];
   out[1] = home_id[1];
   out[2] = home_id[2];
 }
 
+// One thread per active cube: its triangles in table order, vertex ids from the home cubes.
 __global__ void __launch_bounds__(128)
-    mc_face_kernel(const McGeom m, const uint32_t* __restrict__ active,
-                   const unsigned* __restrict__ n_active, const uint32_t* __restrict__ segcnt,
-                   const uint64_t* __restrict__ rowbase, const uint32_t* __restrict__ cinfo,
-                   const IdTables t, int32_t* __restrict__ faces) {
-  const int lane = threadIdx.x & 31;
-  const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (wid >= *n_active) return;
-  const int64_t seg = active[wid];
-  int sx, y, z;
-  seg_coords(m, seg, &sx, &y, &z);
-  const int x = sx * 32 + lane;
-  const unsigned packed = cinfo[(size_t)wid * 32 + lane];
-  const bool act = packed != 0;
-  const int ci = (int)(packed & 0xffu);
-  const unsigned nt = act ? d_ntri[ci] : 0;
-  unsigned inc = nt;
-  for (int o = 1; o < 32; o <<= 1) {
-    const unsigned s = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += s;
-  }
-  int64_t vbase, fbase;
-  seg_base(m, seg, lane, segcnt, rowbase, &vbase, &fbase);
+    mc_face_kernel(const McGeom m, const McLists t, unsigned n_cubes,
+                   const uint2* __restrict__ slot_pre, int32_t* __restrict__ faces) {
+  const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cubes) return;
+  const CubeAt q = cube_at(m, t, c);
+  const int ci = (int)(t.cube_info[c] & 0xffu);
+  const unsigned nt = d_ntri[ci];
   if (nt == 0) return;
-  int64_t fid = fbase + (inc - nt);
+  int64_t fid = slot_pre[q.slot].y;
+  for (unsigned k = 0; k < q.k; k++) fid += d_ntri[t.cube_info[c - q.k + k] & 0xffu];
   // each crossed edge is looked up once, however many triangles share it
   int32_t vid[12];
   unsigned em = d_edge_mask[ci];
@@ -526,9 +574,9 @@ __global__ void __launch_bounds__(128)
     const int e = __ffs(em) - 1;
     em &= em - 1;
     const int a = c_edge_corner[e][0], b = c_edge_corner[e][1];
-    const int hx = x + max(c_corner[a][0], c_corner[b][0]);
-    const int hy = y + max(c_corner[a][1], c_corner[b][1]);
-    const int hz = z + max(c_corner[a][2], c_corner[b][2]);
+    const int hx = q.x + max(c_corner[a][0], c_corner[b][0]);
+    const int hy = q.y + max(c_corner[a][1], c_corner[b][1]);
+    const int hz = q.z + max(c_corner[a][2], c_corner[b][2]);
     const int axis = c_corner[a][0] != c_corner[b][0] ? 0 : (c_corner[a][1] != c_corner[b][1] ? 1 : 2);
     vid[e] = vertex_id_of_edge(m, t, hx, hy, hz, axis);
   }
@@ -599,7 +647,7 @@ namespace {
 // vertices on a slab's top plane to the slab above it.
 __global__ void __launch_bounds__(256)
     mc_export_plane_kernel(const McGeom m, int z, const uint32_t* __restrict__ ibits,
-                           const IdTables t, int32_t* __restrict__ out) {
+                           const McLists t, int32_t* __restrict__ out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t n = (int64_t)m.nx * m.ny;
   if (i >= 2 * n) return;
@@ -632,10 +680,17 @@ __global__ void __launch_bounds__(256)
 #define VCB_TRY(x) \
   if ((e = (x)) != cudaSuccess) return e
 
-static IdTables id_tables(const IsoExtract* st) {
-  IdTables t;
+// Scratch of the sparse passes (IsoExtract): abits = slot_word, active = slot_seg, segcnt = slot_cnt,
+// slot_cube / slot_pre / cube_slot as named, cinfo = cube_info, vb = cube_ids.
+static McLists mc_lists(const IsoExtract* st) {
+  McLists t;
   t.segwid = static_cast<const uint32_t*>(st->segwid.ptr);
-  t.ids3 = static_cast<const int32_t*>(st->vb.ptr);
+  t.slot_seg = static_cast<const uint32_t*>(st->active.ptr);
+  t.slot_word = static_cast<const uint32_t*>(st->abits.ptr);
+  t.slot_cube = static_cast<const uint32_t*>(st->slot_cube.ptr);
+  t.cube_slot = static_cast<const uint32_t*>(st->cube_slot.ptr);
+  t.cube_info = static_cast<const uint32_t*>(st->cinfo.ptr);
+  t.cube_ids = static_cast<const int32_t*>(st->vb.ptr);
   t.hkeys = static_cast<const uint64_t*>(st->hkeys.ptr);
   t.hvals = static_cast<const int32_t*>(st->hvals.ptr);
   t.hmask = st->hmask;
@@ -656,29 +711,26 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
   VCB_TRY(st->ibits.reserve(wbytes));
   VCB_TRY(st->vbits.reserve(wbytes));
   VCB_TRY(st->cbits.reserve(wbytes));
+  // the slot lists are reserved for the worst case (every segment active) and touched sparsely
   VCB_TRY(st->abits.reserve((size_t)m.n_segs * sizeof(uint32_t)));
+  VCB_TRY(st->active.reserve((size_t)m.n_segs * sizeof(uint32_t)));
+  VCB_TRY(st->segwid.reserve((size_t)m.n_segs * sizeof(uint32_t)));
   const int64_t n_rows_owned = (int64_t)g.ny * (g.z_end - g.z_begin);
-  VCB_TRY(st->segcnt.reserve((size_t)m.n_segs * sizeof(uint32_t)));
   // per row of segments: [0, n_rows) counts, then [n_rows + 1 .. ) exclusive prefix + total
   VCB_TRY(st->segbase.reserve((size_t)(2 * n_rows_owned + 2) * sizeof(uint64_t)));
-  VCB_TRY(st->active.reserve((size_t)m.n_segs * sizeof(uint32_t)));
   VCB_TRY(st->counters.reserve(256));
-  VCB_TRY(st->segwid.reserve((size_t)m.n_segs * sizeof(uint32_t)));
   uint32_t* ibits = static_cast<uint32_t*>(st->ibits.ptr);
   uint32_t* vbits = static_cast<uint32_t*>(st->vbits.ptr);
   uint32_t* cbits = static_cast<uint32_t*>(st->cbits.ptr);
-  uint32_t* abits = static_cast<uint32_t*>(st->abits.ptr);
-  uint32_t* segcnt = static_cast<uint32_t*>(st->segcnt.ptr);
   uint64_t* rowcnt = static_cast<uint64_t*>(st->segbase.ptr);
   uint64_t* rowbase = rowcnt + n_rows_owned;
-  uint32_t* active = static_cast<uint32_t*>(st->active.ptr);
-  unsigned* n_active = static_cast<unsigned*>(st->counters.ptr);
+  unsigned* counters = static_cast<unsigned*>(st->counters.ptr);  // slots, cubes, list cursor
   uint32_t* ubits = nullptr;
 
   const size_t plane = (size_t)g.nx * g.ny;
   const float* sdf_stored = g.sdf - (ptrdiff_t)g.halo * (ptrdiff_t)plane;
   const int64_t n_rows = (int64_t)g.ny * (g.z_end - m.zb);
-  VCB_TRY(cudaMemsetAsync(n_active, 0, sizeof(unsigned), stream));
+  VCB_TRY(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned), stream));
   mc_bits_kernel<<<(unsigned)((n_rows + kBitsRows - 1) / kBitsRows), 256, 0, stream>>>(
       sdf_stored, g.nx, m.spr, n_rows, iso_threshold(iso_level), ibits, vbits);
   if (launches) *launches += 1;
@@ -690,26 +742,40 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
     if (launches) *launches += 1;
   }
   mc_cube_kernel<<<(unsigned)((m.n_words + 255) / 256), 256, 0, stream>>>(
-      m, ibits, vbits, ubits, cbits, abits, active, n_active, static_cast<uint32_t*>(st->segwid.ptr));
-  VCB_TRY(cudaMemsetAsync(segcnt, 0, (size_t)m.n_segs * sizeof(uint32_t), stream));
+      m, ibits, vbits, ubits, cbits, static_cast<uint32_t*>(st->active.ptr),
+      static_cast<uint32_t*>(st->abits.ptr), counters, static_cast<uint32_t*>(st->segwid.ptr));
   VCB_TRY(cudaMemsetAsync(rowcnt, 0, (size_t)n_rows_owned * sizeof(uint64_t), stream));
   if (launches) *launches += 1;
-  unsigned h_active = 0;
-  VCB_TRY(cudaMemcpyAsync(&h_active, n_active, sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
+  unsigned h_counts[2] = {0, 0};
+  VCB_TRY(cudaMemcpyAsync(h_counts, counters, sizeof(h_counts), cudaMemcpyDeviceToHost, stream));
   VCB_TRY(cudaStreamSynchronize(stream));
-  st->n_active = h_active;
-  const unsigned wblocks = (h_active + 3) / 4;  // 4 warps per block
-  if (h_active > 0) {
-    VCB_TRY(st->cinfo.reserve((size_t)h_active * 32 * sizeof(uint32_t)));
-    VCB_TRY(st->vb.reserve((size_t)h_active * 32 * 3 * sizeof(int32_t)));
-    mc_count_kernel<<<wblocks, 128, 0, stream>>>(
-        m, ibits, cbits, abits, active, n_active, segcnt,
-        reinterpret_cast<unsigned long long*>(rowcnt), static_cast<uint32_t*>(st->cinfo.ptr));
-    if (launches) *launches += 1;
+  st->n_active = h_counts[0];
+  st->n_cubes = h_counts[1];
+  if (st->n_cubes > 0) {
+    const unsigned ns = st->n_active, nc = st->n_cubes;
+    VCB_TRY(st->slot_cube.reserve((size_t)ns * sizeof(uint32_t)));
+    VCB_TRY(st->segcnt.reserve((size_t)ns * sizeof(uint32_t)));
+    VCB_TRY(st->slot_pre.reserve((size_t)ns * sizeof(uint2)));
+    VCB_TRY(st->cube_slot.reserve((size_t)nc * sizeof(uint32_t)));
+    VCB_TRY(st->cinfo.reserve((size_t)nc * sizeof(uint32_t)));
+    VCB_TRY(st->vb.reserve((size_t)nc * 3 * sizeof(int32_t)));
+    mc_list_kernel<<<(ns + 255) / 256, 256, 0, stream>>>(
+        ns, static_cast<uint32_t*>(st->abits.ptr), counters, static_cast<uint32_t*>(st->slot_cube.ptr),
+        static_cast<uint32_t*>(st->segcnt.ptr), static_cast<uint32_t*>(st->cube_slot.ptr));
+    mc_count_kernel<<<(nc + 255) / 256, 256, 0, stream>>>(
+        m, mc_lists(st), nc, ibits, cbits, static_cast<uint32_t*>(st->cinfo.ptr),
+        static_cast<uint32_t*>(st->segcnt.ptr), reinterpret_cast<unsigned long long*>(rowcnt));
+    if (launches) *launches += 2;
   }
   // the ubits scratch (st->tmp) is dead from here on; the scan reuses st->tmp
   VCB_TRY(scan_exclusive_u64(rowcnt, rowbase, n_rows_owned, rowbase + n_rows_owned, &st->tmp,
                              stream, launches));
+  if (st->n_cubes > 0) {
+    mc_rowprefix_kernel<<<(unsigned)((n_rows_owned * 32 + 255) / 256), 256, 0, stream>>>(
+        m, n_rows_owned, static_cast<uint32_t*>(st->segwid.ptr), static_cast<uint32_t*>(st->segcnt.ptr),
+        reinterpret_cast<unsigned long long*>(rowcnt), rowbase, static_cast<uint2*>(st->slot_pre.ptr));
+    if (launches) *launches += 1;
+  }
   uint64_t total = 0;
   VCB_TRY(cudaMemcpyAsync(&total, rowbase + n_rows_owned, sizeof(total), cudaMemcpyDeviceToHost,
                           stream));
@@ -720,7 +786,7 @@ cudaError_t iso_count(const GridDesc& g, bool un_implied, double iso_level, int 
   return cudaSuccess;
 }
 
-// Phase 2: vertices at their final local index; ids stored in the edge hash are global
+// Phase 2: vertices at their final local index; the ids kept for the face pass are global
 // (local index + vertex_offset).
 cudaError_t iso_emit_vertices(const GridDesc& g, int64_t vertex_offset, IsoExtract* st,
                               cudaStream_t stream, int64_t* launches) {
@@ -738,15 +804,12 @@ cudaError_t iso_emit_vertices(const GridDesc& g, int64_t vertex_offset, IsoExtra
   VCB_TRY(st->verts.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float)));
   VCB_TRY(st->faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int32_t)));
   VCB_TRY(cudaMemsetAsync(st->hkeys.ptr, 0xff, cap * sizeof(uint64_t), stream));
-  if (st->n_active > 0 && nv > 0) {
-    mc_vertex_kernel<<<(st->n_active + 3) / 4, 128, 0, stream>>>(
-        m, g, static_cast<uint32_t*>(st->ibits.ptr), static_cast<uint32_t*>(st->cbits.ptr),
-        static_cast<uint32_t*>(st->abits.ptr), static_cast<uint32_t*>(st->active.ptr),
-        static_cast<unsigned*>(st->counters.ptr), static_cast<uint32_t*>(st->segcnt.ptr),
-        static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin),
-        static_cast<uint32_t*>(st->cinfo.ptr), st->iso_level, st->linear_interp, vertex_offset,
-        static_cast<float*>(st->verts.ptr), static_cast<int32_t*>(st->vb.ptr),
-        static_cast<uint64_t*>(st->hkeys.ptr), static_cast<int32_t*>(st->hvals.ptr), st->hmask);
+  if (st->n_cubes > 0) {
+    mc_vertex_kernel<<<(st->n_cubes + 127) / 128, 128, 0, stream>>>(
+        m, g, mc_lists(st), st->n_cubes, static_cast<uint2*>(st->slot_pre.ptr), st->iso_level,
+        st->linear_interp, vertex_offset, static_cast<float*>(st->verts.ptr),
+        static_cast<int32_t*>(st->vb.ptr), static_cast<uint64_t*>(st->hkeys.ptr),
+        static_cast<int32_t*>(st->hvals.ptr), st->hmask);
     if (launches) *launches += 1;
   }
   st->phase = 2;
@@ -758,7 +821,7 @@ cudaError_t iso_export_top_ids(const GridDesc& g, IsoExtract* st, int32_t* out_d
   if (st->phase < 2) return cudaErrorInvalidValue;
   const int64_t n2 = 2ll * g.nx * g.ny;
   mc_export_plane_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, stream>>>(
-      mc_geom(g), g.z_end - 1, static_cast<uint32_t*>(st->ibits.ptr), id_tables(st), out_dev);
+      mc_geom(g), g.z_end - 1, static_cast<uint32_t*>(st->ibits.ptr), mc_lists(st), out_dev);
   if (launches) *launches += 1;
   return cudaGetLastError();
 }
@@ -779,12 +842,10 @@ cudaError_t iso_emit_faces(const GridDesc& g, IsoExtract* st, cudaStream_t strea
                            int64_t* launches) {
   if (st->phase != 2) return cudaErrorInvalidValue;
   const McGeom m = mc_geom(g);
-  if (st->n_active > 0 && st->n_faces > 0) {
-    mc_face_kernel<<<(st->n_active + 3) / 4, 128, 0, stream>>>(
-        m, static_cast<uint32_t*>(st->active.ptr), static_cast<unsigned*>(st->counters.ptr),
-        static_cast<uint32_t*>(st->segcnt.ptr),
-        static_cast<uint64_t*>(st->segbase.ptr) + (int64_t)g.ny * (g.z_end - g.z_begin),
-        static_cast<uint32_t*>(st->cinfo.ptr), id_tables(st), static_cast<int32_t*>(st->faces.ptr));
+  if (st->n_cubes > 0 && st->n_faces > 0) {
+    mc_face_kernel<<<(st->n_cubes + 127) / 128, 128, 0, stream>>>(
+        m, mc_lists(st), st->n_cubes, static_cast<uint2*>(st->slot_pre.ptr),
+        static_cast<int32_t*>(st->faces.ptr));
     if (launches) *launches += 1;
   }
   st->phase = 3;
