@@ -131,8 +131,8 @@ struct vcb_sharded {
   std::string err;
   // the chunk being collected
   int chunk_cap = kMaxViewsPerLaunch;
-  // After Init() / reset the first chunk is kept small (two views per GPU): nothing can overlap its
-  // transforms and its gather, so the fusion starts sooner; every later chunk is a full launch.
+  // After Init() / reset the first chunk may be kept small (two views per GPU, see queue_view):
+  // nothing can overlap its transforms and its gather, so the fusion starts sooner.
   bool ramp = true;
   int queued = 0, half = 0;
   bool q_device = false;
@@ -572,7 +572,16 @@ int queue_view(vcb_sharded* s, const vcb_view& v, const uint8_t* mask, bool devi
   s->qviews[idx] = v;
   s->qmask[idx] = mask;
   s->queued++;
-  const int cap = (s->ramp && s->world > 1) ? std::min(s->chunk_cap, 2 * s->world) : s->chunk_cap;
+  int cap = s->chunk_cap;
+  if (s->ramp && s->world > 1 && 2 * s->world < s->chunk_cap) {
+    // a small first chunk costs one more launch (one more pass over the slab's state) and saves most
+    // of the first gather, which nothing can hide: worth it when the slabs are thin (many GPUs)
+    // (every rank must take the same decision: the average slab, not this rank's)
+    const double state_s = 16.0 * s->nx * s->ny * ((double)s->nz / s->world) / 6.5e12;
+    const double gather_s = (double)(s->chunk_cap - 2 * s->world) * s->slot_img * (s->world - 1) /
+                            s->world / 7.0e11;
+    if (state_s < 0.5 * gather_s) cap = 2 * s->world;
+  }
   if (s->queued >= cap) return flush_chunk(s);
   return VCB_OK;
 }
