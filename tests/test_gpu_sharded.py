@@ -225,3 +225,24 @@ def test_carve_mask_files_single_and_slabs(cuda_lib, port, tmp_path):
         one.carve_files(cams[:1], paths[:1], (200, 200))
     with pytest.raises(Exception, match="larger than the buffer"):
         one.carve_files(cams[:1], paths[:1], (128, 128))
+
+
+def test_engine_on_two_real_devices_when_present(cuda_lib, port):
+    """ONE process driving two different GPUs (peer copies over NVLink between the devices' pools,
+    cross-device event waits): same checks as with virtual slabs.  Skipped on a single-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    o, opt, cams, masks = scene(n=96, views=70, size=256)
+    orc = oracle_carve(port, opt, cams, masks)
+    ws, wn = orc.download()
+    for devices in ([0, 1], [1, 0, 1]):
+        eng = sharded.LocalSlabs(o, len(devices), devices=devices)
+        assert eng.carve_batch(cams, masks)
+        gs, gn = eng.download_grid()
+        assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+        H.assert_mesh_equal(eng.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)
+        flags, n = eng.occupancy(True)
+        wflags, wcount = orc.occupancy(True)
+        assert n == wcount and np.array_equal(flags, wflags)
+        eng.close()
