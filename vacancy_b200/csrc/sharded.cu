@@ -8,15 +8,18 @@
 //   * single process, a list of devices (vcb_sharded_create): exchanges are peer copies between the
 //     devices (copy engines over NVLink, no SM time), ordered with events.  A device may appear more
 //     than once ("virtual slabs"), which is how the single-GPU tests drive this code.
-//   * one process per GPU (vcb_sharded_create_rank): exchanges are NCCL collectives / send-recv on
-//     the communicator built from a unique id the launcher distributes.  NCCL is resolved with
-//     dlopen("libnccl.so.2") when the first communicator is made - a process that already loaded
-//     NCCL (torch) shares it, a single-GPU host never needs it.
+//   * one process per GPU (vcb_sharded_create_rank): the small exchanges (halo planes, counts, id
+//     planes, mesh parts) are NCCL collectives / send-recv on the communicator built from a unique
+//     id the launcher distributes; the bulk - the SDF images - is pulled by the copy engines from
+//     the other ranks' pools, mapped once with CUDA IPC, with a tiny NCCL all-gather as the signal
+//     (see "the pools of the other ranks" below).  NCCL is resolved with dlopen("libnccl.so.2")
+//     when the first communicator is made - a process that already loaded NCCL (torch) shares
+//     it, a single-GPU host never needs it.
 //
 // Carving, per chunk of <= 64 views (one fusion launch):
 //   1. view i of the chunk belongs to rank i mod N: only that rank receives the mask (its own PCIe
 //      link) and runs the 2D SDF kernels (voxel_carver.cc:169-237) for it, on a side stream;
-//   2. the float SDF images, their 8x8-block flags and their maxima are all-gathered into every
+//   2. the float SDF images, their 8x8-block flags and their maxima are gathered into every
 //      rank's pool (rank r's results occupy slots [r*J, (r+1)*J), J = ceil(views / N));
 //   3. every rank fuses all views of the chunk into its slab (voxel_carver.cc:415-496), in call
 //      order, on its main stream.
