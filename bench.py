@@ -202,18 +202,29 @@ def run_ours(args, cfg):
 
     from vacancy_b200 import sharded
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
+    procs = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device - this library has no CPU fallback")
     torch.cuda.set_device(local)
-    if world > 1:
+    if procs > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # `world` = number of z slabs = GPUs.  Launched by torch.distributed.run: one process per GPU
+    # (vcb_sharded_create_rank).  Launched plainly with --gpus N > 1: ONE process drives the N GPUs
+    # (vcb_sharded_create - what a C++ host gets through VACANCY_B200_DEVICES).
+    single_process = procs == 1 and args.gpus > 1
+    world = args.gpus if single_process else procs
+    if single_process and torch.cuda.device_count() < world:
+        raise SystemExit("bench.py: --gpus %d but %d CUDA devices" % (world, torch.cuda.device_count()))
     n, V, size = cfg["grid"], cfg["views"], cfg["image"]
     hbm_peak, peak_src, _ = load_peaks()
 
-    car = sharded.ShardedCarver(S.grid_option(n, weighted=cfg["weighted"]), rank, world, local)
+    if single_process:
+        car = sharded.LocalSlabs(S.grid_option(n, weighted=cfg["weighted"]), world,
+                                 devices=list(range(world)))
+    else:
+        car = sharded.ShardedCarver(S.grid_option(n, weighted=cfg["weighted"]), rank, world, local)
     # the engine orders a slab's reset / fusion / extraction on its own main stream: time on it
     stream = torch.cuda.ExternalStream(car.main_stream(0), device=torch.device("cuda", local))
     cams = S.circle_cameras(V, size)
@@ -226,9 +237,10 @@ def run_ours(args, cfg):
     torch.cuda.synchronize()
 
     def barrier():
-        if world > 1:
+        if procs > 1:
             dist.barrier()
-        torch.cuda.synchronize()
+        for d in (range(world) if single_process else [local]):
+            torch.cuda.synchronize(d)
 
     packed_dev = car.pack_masks([dev_masks.data_ptr() + i * dev_masks.stride(0) for i in range(V)])
     packed_views = car.pack_views(views)
@@ -264,7 +276,7 @@ def run_ours(args, cfg):
         e1.record(stream)
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-        if world > 1:
+        if procs > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item()), out
 
@@ -274,12 +286,16 @@ def run_ours(args, cfg):
         # the slabs do not cost the same (edge slabs see the cameras differently): re-partition once
         # from the measured fusion time of the warm-up passes, then warm up again
         for _ in range(2):  # second round refines the first estimate
-            ranges = car.rebalance(car.stage_times()["fusion"][0])
+            if single_process:
+                ranges = car.rebalance()
+            else:
+                ranges = car.rebalance(car.stage_times()["fusion"][0])
             for _ in range(args.warmup):
                 step_resident()
     else:
         ranges = car.ranges
-    car.stage_times()  # clear the per-stage counters
+    for i in range(car.n_local):
+        car.stage_times(i)  # clear the per-stage counters
     car.car.fusion_class_counts()  # ... and the tile-class counters
     sampler = ClockSampler(local)
     if rank == 0:
@@ -287,6 +303,7 @@ def run_ours(args, cfg):
     ms_total, counts = timed(step_resident, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     stages = car.stage_times()
+    other_stages = [car.stage_times(i) for i in range(1, car.n_local)]
     classes = car.car.fusion_class_counts()  # (tile, view) pairs of this rank's launches, by class
     # one more pass, untimed, with the kernel counting the view iterations its warps execute (the
     # counting costs ~1 % of the kernel's time, so it stays out of the timed region)
@@ -294,10 +311,16 @@ def run_ours(args, cfg):
     step_resident()
     iters = car.car.fusion_class_counts()["warp_iterations"]
     car.car.set_statistics(False)
-    car.stage_times()
+    for i in range(car.n_local):
+        car.stage_times(i)
     ms_step = ms_total / args.steps
     per_rank = None
-    if world > 1:  # how evenly the slabs split the work (rank order = slab order, bottom to top)
+    if single_process:
+        alls = [stages] + other_stages
+        per_rank = {k + "_ms": [round(st[name][0] / args.steps, 2) for st in alls]
+                    for k, name in (("fusion", "fusion"), ("sdf2d", "sdf2d"),
+                                    ("marching_cubes", "marching_cubes"))}
+    elif world > 1:  # how evenly the slabs split the work (rank order = slab order, bottom to top)
         mine = torch.tensor([stages["fusion"][0] / args.steps, stages["sdf2d"][0] / args.steps,
                              stages["marching_cubes"][0] / args.steps], device="cuda")
         allr = [torch.empty_like(mine) for _ in range(world)]
@@ -420,7 +443,8 @@ def run_ours(args, cfg):
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": describe(cfg), "grid": [n, n, n], "views": V, "image": [size, size],
-                   "parallelism": "z-slab x%d" % world,
+                   "parallelism": "z-slab x%d, %s" % (world, "one process driving all GPUs"
+                                                       if single_process else "one process per GPU"),
                    "slabs": [list(r) for r in ranges],
                    "l2": "inputs larger than L2 (masks %.2f GB, grid state %.2f GB per step)"
                          % (V * size * size / 1e9, 8 * nvox / 1e9),
@@ -461,7 +485,7 @@ def run_ours(args, cfg):
     if rank == 0:
         print(json.dumps(line))
     car.close()  # every rank at the same point: the ranks unmap each other's buffers before freeing
-    if world > 1:
+    if procs > 1:
         dist.destroy_process_group()
 
 

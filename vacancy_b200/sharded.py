@@ -289,6 +289,25 @@ class LocalSlabs(_Engine):
         self._h = h
         self._after_create(option)
 
+    @property
+    def car(self):
+        return self.slabs[0]
+
+    @property
+    def slab_voxels(self):
+        return self.slabs[0].slab_voxels
+
+    def rebalance(self):
+        """Re-partitions the grid so that every slab carries about the same fusion time, measured
+        since the last call of stage_times (the grid state is discarded, like Init())."""
+        cost = [self.stage_times(i)["fusion"][0] for i in range(self.n_local)]
+        new = rebalanced_ranges(self.ranges, cost, quantum=FUSION_TILE_PLANES)
+        if new != self.ranges:
+            self.slabs = []
+            self._check(self._lib.vcb_sharded_repartition(self._h, _bounds_array(new)))
+            self._refresh()
+        return self.ranges
+
     def download_grid(self):
         self.flush()
         parts = [s.download_grid() for s in self.slabs]
