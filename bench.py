@@ -280,6 +280,9 @@ def run_ours(args, cfg):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item()), out
 
+    if args.auto_balance and world > 1:
+        car.set_auto_balance(True)
+        args.no_rebalance = True
     for _ in range(args.warmup):
         step_resident()
     if world > 1 and not args.no_rebalance:
@@ -499,6 +502,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-rebalance", action="store_true",
                     help="keep the equal-thickness z slabs (multi-GPU)")
+    ap.add_argument("--auto-balance", action="store_true",
+                    help="no measured re-partitioning: the engine places the slab boundaries itself "
+                         "from the tile classes of the first chunk of views (multi-GPU)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     cfg = workload(args.workload)

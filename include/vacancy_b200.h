@@ -347,6 +347,14 @@ const char* vcb_sharded_last_error(const vcb_sharded* s);
 int vcb_sharded_info(const vcb_sharded* s, int32_t* world, int32_t* n_local, int32_t dims3[3]);
 int vcb_sharded_bounds(const vcb_sharded* s, int32_t* z_bounds /* world + 1 */);
 int vcb_sharded_repartition(vcb_sharded* s, const int32_t* z_bounds);
+/* Slabs of equal thickness do not cost the same (the ends of the grid see less of the object).  With
+ * auto-balance on, the engine places the boundaries itself when the first chunk of views (up to 64)
+ * of a fresh grid arrives: it classifies every fusion tile of the whole grid against those views
+ * (the classification the fusion kernel uses anyway, milliseconds), sums a cost per layer of 8
+ * planes and cuts at equal cost - before anything is fused, so only buffers are re-created.  Call
+ * it before the first carve call; handles from vcb_sharded_local are invalid after that first
+ * carve call and must be fetched again.  Every rank makes the same call. */
+int vcb_sharded_set_auto_balance(vcb_sharded* s, int32_t enabled);
 /* i-th slab held by THIS process (0 <= i < n_local) and its rank: the carver handle serves
  * vcb_download_grid, vcb_grid_device, vcb_ply_body_*, ... on that slab; do not carve through it. */
 int vcb_sharded_local(vcb_sharded* s, int32_t i, vcb_carver** carver, int32_t* rank);

@@ -246,3 +246,32 @@ def test_engine_on_two_real_devices_when_present(cuda_lib, port):
         wflags, wcount = orc.occupancy(True)
         assert n == wcount and np.array_equal(flags, wflags)
         eng.close()
+
+
+def test_engine_auto_balance_places_boundaries_and_keeps_the_result(cuda_lib, port):
+    """vcb_sharded_set_auto_balance: the boundaries move (whole fusion tiles of 8 planes, the ends of
+    the grid get thicker slabs than the middle, which sees the object) before the first chunk is
+    fused - and the result is still the oracle's, bit for bit."""
+    n = 256  # a small object low in the grid: the upper layers only ever see the 1.0 plateau
+    o = S.grid_option(n, weighted=True)
+    opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True, band=0.1)
+    cams = S.circle_cameras(70, 512, tilt=0.2)
+    masks = [S.silhouette(c, ((0.1, 0.0, -0.55, 0.3),)) for c in cams]
+    orc = oracle_carve(port, opt, cams, masks)
+    ws, wn = orc.download()
+    eng = sharded.LocalSlabs(o, 4)
+    equal = [(0, 64), (64, 128), (128, 192), (192, 256)]
+    assert eng.ranges == equal
+    eng.set_auto_balance(True)
+    assert eng.carve_batch(cams, masks)
+    moved = eng.ranges
+    assert moved != equal
+    assert all(a % 8 == 0 and b % 8 == 0 and b - a >= 8 for a, b in moved)
+    assert moved[0][0] == 0 and moved[-1][1] == n
+    assert moved[3][1] - moved[3][0] > moved[0][1] - moved[0][0]  # the cheap end gets more planes
+    gs, gn = eng.download_grid()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)
+    H.assert_mesh_equal(eng.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)
+    # a later pass keeps the partition
+    eng.reset()
+    assert eng.carve_batch(cams[:5], masks[:5]) and eng.ranges == moved

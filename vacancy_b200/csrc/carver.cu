@@ -294,6 +294,49 @@ int fuse_prepared(vcb_carver* c, int n, const vcb_view* views, const float* cons
   return flush_pending(c);
 }
 
+// Cost estimate per z tile layer of the WHOLE grid for the given prepared views (on this carver's
+// device and stream; nothing is fused).  Used by the z-slab engine to place the slab boundaries.
+int layer_costs(vcb_carver* c, int n, const vcb_view* views, const float* const* images,
+                const uint32_t* const* tiles, const float* const* max_sdf,
+                std::vector<uint64_t>* cost) {
+  if (n < 1 || n > kMaxViewsPerLaunch) return fail(c, VCB_ERR_INVALID, "layer_costs: %d views", n);
+  int rc = use_device(c, c->opt.device);
+  if (rc != VCB_OK) return rc;
+  FuseParams p = c->fp;
+  p.z_begin = 0;
+  p.z_end = c->nz;
+  p.n_views = n;
+  const bool flags = c->use_tiles && c->opt.sdf_interp == VCB_INTERP_BILINEAR;
+  for (int i = 0; i < n; i++) {
+    FuseView& f = p.views[i];
+    fill_fuse_view(&f, views[i], images[i], max_sdf[i]);
+    if (flags && tiles && tiles[i]) {
+      f.tiles = tiles[i];
+      f.tile_words = tile_words_for(views[i].width);
+      f.tile_rows = tile_rows_for(views[i].height);
+    }
+  }
+  const int layers = (c->nz + fusion_tile_planes() - 1) / fusion_tile_planes();
+  Scratch tabs, dev_cost;
+  CU(c, tabs.reserve(fusion_table_bytes(c->nx, c->ny, c->nz)));
+  cudaError_t e = dev_cost.reserve((size_t)layers * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemsetAsync(dev_cost.ptr, 0, (size_t)layers * sizeof(unsigned long long), c->stream);
+  if (e == cudaSuccess) {
+    p.tables = static_cast<unsigned char*>(tabs.ptr);
+    launch_layer_costs(p, c->opt.sdf_interp, static_cast<unsigned long long*>(dev_cost.ptr), c->stream);
+    e = cudaGetLastError();
+  }
+  cost->assign(layers, 0);
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(cost->data(), dev_cost.ptr, (size_t)layers * sizeof(uint64_t),
+                        cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  tabs.release();
+  dev_cost.release();
+  if (e != cudaSuccess) return fail(c, VCB_ERR_CUDA, "layer_costs: %s", cudaGetErrorString(e));
+  return VCB_OK;
+}
+
 int ensure_pool(vcb_carver* c, size_t floats_per_image) {
   if (floats_per_image <= c->slot_floats && c->pool.ptr) return VCB_OK;
   int rc = flush_pending(c);

@@ -102,6 +102,11 @@ int decode_mask_batch(const char* const* paths, const vcb_view* views, int n, co
 int fuse_prepared(vcb_carver* c, int n, const vcb_view* views, const float* const* images,
                   const uint32_t* const* tiles, const float* const* max_sdf);
 
+// cost per z tile layer (fusion_tile_planes() planes each) of the whole grid for prepared views
+int layer_costs(vcb_carver* c, int n, const vcb_view* views, const float* const* images,
+                const uint32_t* const* tiles, const float* const* max_sdf,
+                std::vector<uint64_t>* cost);
+
 // CUDA-event span around kernels of one stage (0 2D SDF, 1 fusion, 2 ExtractVoxel, 3 marching
 // cubes) on `stream` (default: the carver's); summed by vcb_stage_times
 struct Span {

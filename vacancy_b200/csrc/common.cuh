@@ -83,6 +83,9 @@ struct FuseParams {
   FuseView views[kMaxViewsPerLaunch];
 };
 size_t fusion_table_bytes(int nx, int ny, int nz_slab);
+int fusion_tile_planes();  // z planes per fusion tile: a slab pays for whole tiles
+void launch_layer_costs(FuseParams& p, int interp, unsigned long long* layer_cost,
+                        cudaStream_t stream);
 
 // ---- per-view descriptor of the 2D SDF kernels (device array) ----
 struct SdfView {

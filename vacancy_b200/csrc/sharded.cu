@@ -137,6 +137,10 @@ struct vcb_sharded {
   // After Init() / reset the first chunk may be kept small (two views per GPU, see queue_view):
   // nothing can overlap its transforms and its gather, so the fusion starts sooner.
   bool ramp = true;
+  // vcb_sharded_set_auto_balance: before the first chunk is fused the slab boundaries are placed
+  // from a cost estimate of that chunk's tile classes (the grid holds nothing yet, so moving the
+  // boundaries costs a re-allocation, not a migration)
+  bool balance_pending = false;
   int queued = 0, half = 0;
   bool q_device = false;
   vcb_view qviews[kMaxViewsPerLaunch];
@@ -413,6 +417,62 @@ int ensure_buffers(vcb_sharded* s, int w, int h) {
   return VCB_OK;
 }
 
+// Slab boundaries from the tile classes of the chunk that has just been gathered (half `h`, `cnt`
+// views, J slots per rank).  Every process computes the same integer costs from the same images, so
+// all ranks arrive at the same boundaries without talking to each other.  The grid must still be
+// fresh: the carvers are simply re-created on the new plane ranges.
+int place_boundaries(vcb_sharded* s, int cnt, int J, int h) {
+  const int N = s->world, q = fusion_tile_planes();
+  const int layers = (s->nz + q - 1) / q;
+  if (layers < 2 * N) return VCB_OK;  // too thin to place anything
+  ShardRank& L = s->local[0];
+  SCU(s, cudaSetDevice(L.device));
+  SCU(s, cudaStreamSynchronize(L.side));  // this chunk's images, flags and maxima are in the pool
+  const float* images[kMaxViewsPerLaunch];
+  const uint32_t* tiles[kMaxViewsPerLaunch];
+  const float* maxs[kMaxViewsPerLaunch];
+  for (int idx = 0; idx < cnt; idx++) {
+    const int slot = (idx % N) * J + idx / N;
+    images[idx] = reinterpret_cast<const float*>(static_cast<unsigned char*>(L.img[h].ptr) +
+                                                 (size_t)slot * s->slot_img);
+    tiles[idx] = reinterpret_cast<const uint32_t*>(static_cast<unsigned char*>(L.tiles[h].ptr) +
+                                                   (size_t)slot * s->slot_tiles);
+    maxs[idx] = static_cast<const float*>(L.maxs[h].ptr) + slot;
+  }
+  std::vector<uint64_t> cost;
+  SCAR(s, L, layer_costs(L.car, cnt, s->qviews, images, tiles, maxs, &cost));
+  uint64_t total = 0;
+  for (uint64_t c : cost) total += c;
+  if (env_flag("VACANCY_B200_DEBUG_BALANCE", false)) {
+    fprintf(stderr, "vacancy_b200: cost per layer of %d planes (rank %d):", q, L.rank);
+    for (uint64_t c : cost) fprintf(stderr, " %llu", (unsigned long long)c);
+    fprintf(stderr, "\n");
+  }
+  if (total == 0) return VCB_OK;
+  std::vector<int> b(N + 1, 0);
+  b[N] = s->nz;
+  uint64_t run = 0;
+  int layer = 0;
+  for (int r = 1; r < N; r++) {
+    // first layer boundary at which the running cost reaches r / N of the total (or the one before
+    // it, whichever is closer), leaving at least one layer to every slab still to come
+    const uint64_t target = total / N * r;
+    while (layer < layers && run + cost[layer] <= target) run += cost[layer++];
+    int k = layer;
+    if (k < layers && target - run > run + cost[k] - target) k++;
+    const int lo = b[r - 1] / q + 1, hi = layers - (N - r);
+    k = k < lo ? lo : (k > hi ? hi : k);
+    b[r] = k * q;
+    while (layer < k) run += cost[layer++];
+  }
+  if (b == s->bounds) return VCB_OK;
+  int rc = check_bounds(s, b);
+  if (rc != VCB_OK) return rc;
+  destroy_carvers(s);
+  s->bounds = b;
+  return create_carvers(s);
+}
+
 // steps 1-3 of the header comment for the views collected so far
 int flush_chunk(vcb_sharded* s) {
   const int cnt = s->queued;
@@ -529,6 +589,12 @@ int flush_chunk(vcb_sharded* s) {
       }
     }
   }
+  // ---- 2b. first chunk of a fresh engine with auto-balance: place the slab boundaries ----
+  if (s->balance_pending && N > 1) {
+    s->balance_pending = false;
+    int rc = place_boundaries(s, cnt, J, h);
+    if (rc != VCB_OK) return rc;
+  }
   // ---- 3. every slab fuses the whole chunk, in call order ----
   for (auto& L : s->local) {
     SCU(s, cudaSetDevice(L.device));
@@ -576,7 +642,7 @@ int queue_view(vcb_sharded* s, const vcb_view& v, const uint8_t* mask, bool devi
   s->qmask[idx] = mask;
   s->queued++;
   int cap = s->chunk_cap;
-  if (s->ramp && s->world > 1 && 2 * s->world < s->chunk_cap) {
+  if (s->ramp && !s->balance_pending && s->world > 1 && 2 * s->world < s->chunk_cap) {
     // a small first chunk costs one more launch (one more pass over the slab's state) and saves most
     // of the first gather, which nothing can hide: worth it when the slabs are thin (many GPUs)
     // (every rank must take the same decision: the average slab, not this rank's)
@@ -878,6 +944,12 @@ int vcb_sharded_local(vcb_sharded* s, int32_t i, vcb_carver** carver, int32_t* r
   if (!s || i < 0 || i >= (int)s->local.size()) return sfail(s, VCB_ERR_INVALID, "no such local slab");
   if (carver) *carver = s->local[i].car;
   if (rank) *rank = s->local[i].rank;
+  return VCB_OK;
+}
+
+int vcb_sharded_set_auto_balance(vcb_sharded* s, int32_t enabled) {
+  if (!s) return sfail(nullptr, VCB_ERR_INVALID, "null handle");
+  s->balance_pending = enabled != 0;
   return VCB_OK;
 }
 

@@ -143,6 +143,22 @@ class _Engine:
             self.slabs.append(VoxelCarver.borrowed(h.value, self._option))
             self.local_ranks.append(r.value)
 
+    def set_auto_balance(self, enabled=True):
+        """Let the engine place the slab boundaries itself from the first chunk of views of a fresh
+        grid (vcb_sharded_set_auto_balance); call before the first carve."""
+        self._check(self._lib.vcb_sharded_set_auto_balance(self._h, int(bool(enabled))))
+        self._auto_balance = bool(enabled)
+
+    def _refresh_if_moved(self):
+        # with auto-balance the first carve call may re-create the slabs on other boundaries
+        if getattr(self, "_auto_balance", False):
+            b = (C.c_int32 * (self.world + 1))()
+            self._check(self._lib.vcb_sharded_bounds(self._h, b))
+            if [(b[i], b[i + 1]) for i in range(self.world)] != self.ranges:
+                self.slabs = []
+                self._refresh()
+            self._auto_balance = False  # placed once
+
     def close(self):
         if getattr(self, "_h", None):
             self.slabs = []
@@ -172,6 +188,7 @@ class _Engine:
         fn = (self._lib.vcb_sharded_carve_masks_device if device
               else self._lib.vcb_sharded_carve_masks)
         self._check(fn(self._h, n, arr, ptrs, None))
+        self._refresh_if_moved()
 
     def carve_files(self, cameras, paths, size, n_threads=0):
         """Silhouette FILES of `size` = (width, height) (vcb_sharded_carve_mask_files): every
@@ -180,6 +197,7 @@ class _Engine:
         views = (capi.View * n)(*[make_view(c, size[0], size[1]) for c in cameras])
         arr = (C.c_char_p * n)(*[str(p).encode() for p in paths])
         self._check(self._lib.vcb_sharded_carve_mask_files(self._h, n, views, arr, int(n_threads)))
+        self._refresh_if_moved()
         return True
 
     @staticmethod
