@@ -252,11 +252,16 @@ def test_engine_auto_balance_places_boundaries_and_keeps_the_result(cuda_lib, po
     """vcb_sharded_set_auto_balance: the boundaries move (whole fusion tiles of 8 planes, the ends of
     the grid get thicker slabs than the middle, which sees the object) before the first chunk is
     fused - and the result is still the oracle's, bit for bit."""
-    n = 256  # a small object low in the grid: the upper layers only ever see the 1.0 plateau
+    from vacancy_b200 import PinholeCamera
+    n = 256
     o = S.grid_option(n, weighted=True)
     opt = B.make_options(o.bb_min, o.bb_max, o.resolution, update=1, truncation=True, band=0.1)
-    cams = S.circle_cameras(70, 512, tilt=0.2)
-    masks = [S.silhouette(c, ((0.1, 0.0, -0.55, 0.3),)) for c in cams]
+    # long lenses on a turntable: the images cover only the middle of the grid, so the tiles of the
+    # first and last z layers project outside the image in most views (skipped, cheap) and the
+    # middle layers carry the work - the end slabs must come out thicker
+    cams = [PinholeCamera(512, 512, c.c2w(), c.principal_point(), (3.5 * 512, 3.5 * 512))
+            for c in S.circle_cameras(70, 512, tilt=0.2)]
+    masks = [S.silhouette(c, S.DUMBBELL) for c in cams]
     orc = oracle_carve(port, opt, cams, masks)
     ws, wn = orc.download()
     eng = sharded.LocalSlabs(o, 4)
@@ -268,7 +273,8 @@ def test_engine_auto_balance_places_boundaries_and_keeps_the_result(cuda_lib, po
     assert moved != equal
     assert all(a % 8 == 0 and b % 8 == 0 and b - a >= 8 for a, b in moved)
     assert moved[0][0] == 0 and moved[-1][1] == n
-    assert moved[3][1] - moved[3][0] > moved[0][1] - moved[0][0]  # the cheap end gets more planes
+    assert moved[0][1] - moved[0][0] > moved[1][1] - moved[1][0]  # the cheap end gets more planes
+    assert moved[3][1] - moved[3][0] > moved[2][1] - moved[2][0]
     gs, gn = eng.download_grid()
     assert np.array_equal(gn, wn) and bits_equal(gs, ws)
     H.assert_mesh_equal(eng.extract_iso(), orc.extract_iso(), o.bb_min, o.bb_max)

@@ -141,6 +141,7 @@ struct vcb_sharded {
   // from a cost estimate of that chunk's tile classes (the grid holds nothing yet, so moving the
   // boundaries costs a re-allocation, not a migration)
   bool balance_pending = false;
+  bool probing = false;  // the chunk being collected is a sample for the estimate, not to be fused
   int queued = 0, half = 0;
   bool q_device = false;
   vcb_view qviews[kMaxViewsPerLaunch];
@@ -589,9 +590,19 @@ int flush_chunk(vcb_sharded* s) {
       }
     }
   }
-  // ---- 2b. first chunk of a fresh engine with auto-balance: place the slab boundaries ----
+  // ---- 2b. auto-balance: place the slab boundaries from this chunk's tile classes ----
   if (s->balance_pending && N > 1) {
     s->balance_pending = false;
+    if (s->probing) {
+      // a sample of the views of a long call: estimate, then forget the chunk (its views come
+      // again, in call order); nothing may still be reading the pools when they are reused
+      for (auto& L : s->local) {
+        SCU(s, cudaSetDevice(L.device));
+        SCU(s, cudaStreamSynchronize(L.side));
+      }
+      s->queued = 0;
+      return place_boundaries(s, cnt, J, h);
+    }
     int rc = place_boundaries(s, cnt, J, h);
     if (rc != VCB_OK) return rc;
   }
@@ -661,6 +672,25 @@ int carve_impl(vcb_sharded* s, int32_t n_views, const vcb_view* views, const uin
   if (n_views < 0 || (n_views > 0 && (!views || !masks))) return sfail(s, VCB_ERR_INVALID, "null argument");
   bool want_sdf = false;
   for (int i = 0; sdf_out && i < n_views; i++) want_sdf = want_sdf || sdf_out[i] != nullptr;
+  if (s->balance_pending && s->world > 1 && n_views > s->chunk_cap && s->queued == 0 && !want_sdf) {
+    // Auto-balance with many views in one call: the first chunk alone may see the grid from one
+    // side only (a turntable's first 64 views), so the estimate uses views spread over the call.
+    s->probing = true;
+    int rc = VCB_OK;
+    for (int k = 0; k < s->chunk_cap && rc == VCB_OK; k++) {
+      const int i = (int)((int64_t)k * n_views / s->chunk_cap);
+      rc = queue_view(s, views[i], masks[i], device_io);  // the last one flushes (probe branch)
+    }
+    s->probing = false;
+    s->queued = 0;
+    if (rc != VCB_OK) return rc;
+    if (!device_io) {
+      for (auto& L : s->local) {
+        SCU(s, cudaSetDevice(L.device));
+        SCU(s, cudaStreamSynchronize(L.copy));
+      }
+    }
+  }
   for (int i = 0; i < n_views; i++) {
     if (want_sdf && sdf_out[i]) {
       // the caller wants this view's 2D SDF back (the reference's `Image1f* sdf`): the view gets a
