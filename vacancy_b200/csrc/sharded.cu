@@ -1041,6 +1041,7 @@ int vcb_sharded_carve_sdfs(vcb_sharded* s, int32_t n_views, const vcb_view* view
   // carved before them (the slab's own queue keeps the call order)
   int rc = flush_chunk(s);
   if (rc != VCB_OK) return rc;
+  s->balance_pending = false;  // the grid is no longer empty: the boundaries stay where they are
   for (auto& L : s->local) SCAR(s, L, vcb_carve_sdfs(L.car, n_views, views, sdfs));
   return VCB_OK;
 }
@@ -1310,6 +1311,7 @@ int vcb_sharded_load_grid(vcb_sharded* s, const char* const* paths, int32_t n_pa
   DeviceGuard restore_callers_device;
   int rc = flush_chunk(s);
   if (rc != VCB_OK) return rc;
+  s->balance_pending = false;  // a restored grid must not be re-partitioned away
   s->iso_phase = 0;
   s->total_vox = -1;
   return for_each_local(s, [&](ShardRank& L) {

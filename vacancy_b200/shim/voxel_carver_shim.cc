@@ -20,7 +20,8 @@
 // Placement comes from the environment, so that host code needs no change to use more GPUs:
 //   VACANCY_B200_DEVICE=<n>        the one GPU to run on (default 0);
 //   VACANCY_B200_DEVICES=0,1,2,3   carve ONE grid on several GPUs (z slabs, vcb_sharded_*): same
-//                                  calls, same results, the mesh arrives whole.
+//                                  calls, same results, the mesh arrives whole; the engine places
+//                                  the slab boundaries itself (VACANCY_B200_AUTO_BALANCE=0: equal).
 #include "vacancy/voxel_carver.h"
 
 #include <cstdio>
@@ -300,6 +301,10 @@ bool VoxelCarver::Init() {  // voxel_carver.cc:375-392; calling it again re-crea
                                    &h.many),
                 "VoxelCarver::Init"))
       return false;
+    // host code written for the reference cannot re-balance the slabs: let the engine place the
+    // boundaries itself when the first views arrive (VACANCY_B200_AUTO_BALANCE=0 keeps them equal)
+    const char* ab = std::getenv("VACANCY_B200_AUTO_BALANCE");
+    vcb_sharded_set_auto_balance(h.many, (ab != nullptr && ab[0] == '0') ? 0 : 1);
   } else {
     if (devices.size() == 1) o.device = devices[0];
     if (!report(nullptr, vcb_create(&o, &h.one), "VoxelCarver::Init")) return false;
