@@ -355,6 +355,11 @@ int vcb_sharded_repartition(vcb_sharded* s, const int32_t* z_bounds);
  * it before the first carve call; handles from vcb_sharded_local are invalid after that first
  * carve call and must be fetched again.  Every rank makes the same call. */
 int vcb_sharded_set_auto_balance(vcb_sharded* s, int32_t enabled);
+/* The cut itself (host only, no GPU): world + 1 plane indices such that every slab carries about
+ * total / world of the layer costs, on whole layers of planes_per_layer planes (the last layer may
+ * be short: n_layers = ceil(nz / planes_per_layer)), at least one layer per slab. */
+int vcb_balance_bounds(const uint64_t* layer_cost, int32_t n_layers, int32_t planes_per_layer,
+                       int32_t nz, int32_t world, int32_t* z_bounds);
 /* i-th slab held by THIS process (0 <= i < n_local) and its rank: the carver handle serves
  * vcb_download_grid, vcb_grid_device, vcb_ply_body_*, ... on that slab; do not carve through it. */
 int vcb_sharded_local(vcb_sharded* s, int32_t i, vcb_carver** carver, int32_t* rank);

@@ -85,3 +85,35 @@ def test_count_exchange_world2_gloo():
     for rank, off, total, uid in res:
         assert off == [[0, 0], [100, 7]] and total == [300, 15]
     assert len(res[0][3]) == 128 and res[0][3] == res[1][3] and any(res[0][3])
+
+
+def test_balance_bounds_host_only():
+    """vcb_balance_bounds: the cut the engine's auto-balance makes from its per-layer costs (no GPU
+    needed): equal costs give equal slabs, cheap ends give thick end slabs, every slab keeps a
+    layer, boundaries are whole layers, a short last layer is allowed."""
+    import ctypes as C
+    from vacancy_b200 import capi
+    lib = capi.load_library()
+
+    def cut(cost, ppl, nz, world):
+        arr = (C.c_uint64 * len(cost))(*[int(c) for c in cost])
+        out = (C.c_int32 * (world + 1))()
+        rc = lib.vcb_balance_bounds(arr, len(cost), ppl, nz, world, out)
+        return rc, list(out)
+
+    assert cut([10] * 128, 8, 1024, 8) == (0, [0, 128, 256, 384, 512, 640, 768, 896, 1024])
+    # the shape measured on cfg4: the ends cost more per plane than the middle
+    cost = [120] * 32 + [100] * 64 + [120] * 32
+    rc, b = cut(cost, 8, 1024, 8)
+    sizes = [b[i + 1] - b[i] for i in range(8)]
+    assert rc == 0 and b[0] == 0 and b[-1] == 1024 and all(x % 8 == 0 for x in b)
+    assert sizes[0] < sizes[3] and sizes[7] < sizes[4] and sizes == sizes[::-1]
+    per_slab = [sum(cost[b[i] // 8:b[i + 1] // 8]) for i in range(8)]
+    assert max(per_slab) - min(per_slab) <= 2 * 120  # within a layer or two of each other
+    # all the cost in one layer: the others still get one layer each
+    rc, b = cut([0, 0, 1000, 0, 0, 0], 8, 42, 3)
+    assert rc == 0 and b[0] == 0 and b[-1] == 42 and b[1] >= 8 and b[2] - b[1] >= 8 and b[2] <= 40
+    # short last layer (42 planes = 5 full layers + 2 planes), and refused arguments
+    assert cut([1] * 6, 8, 42, 2)[1] == [0, 24, 42]
+    assert cut([1] * 6, 8, 48, 7)[0] == -1     # fewer layers than slabs
+    assert cut([1] * 5, 8, 42, 2)[0] == -1     # layer count does not match nz

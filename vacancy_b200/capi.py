@@ -55,7 +55,7 @@ EXPORTS = [
     "vcb_ply_header", "vcb_ply_body_size", "vcb_ply_body_fill", "vcb_ply_format",
     "vcb_sharded_create", "vcb_sharded_unique_id", "vcb_sharded_create_rank", "vcb_sharded_destroy",
     "vcb_sharded_last_error", "vcb_sharded_info", "vcb_sharded_bounds", "vcb_sharded_repartition",
-    "vcb_sharded_local", "vcb_sharded_stream", "vcb_sharded_set_auto_balance", "vcb_sharded_reset", "vcb_sharded_carve_masks",
+    "vcb_sharded_local", "vcb_sharded_stream", "vcb_sharded_set_auto_balance", "vcb_balance_bounds", "vcb_sharded_reset", "vcb_sharded_carve_masks",
     "vcb_sharded_carve_masks_device", "vcb_sharded_carve_sdfs", "vcb_sharded_flush", "vcb_sharded_synchronize",
     "vcb_sharded_extract_iso_count", "vcb_sharded_extract_iso_fill", "vcb_sharded_local_mesh",
     "vcb_sharded_extract_voxel_count", "vcb_sharded_extract_voxel_fill", "vcb_sharded_stage_times",
@@ -153,6 +153,7 @@ def load_library(path=LIB_PATH):
     L.vcb_sharded_local.argtypes = [vp, i32, C.POINTER(vp), ip]
     L.vcb_sharded_stream.argtypes = [vp, i32, C.POINTER(vp)]
     L.vcb_sharded_set_auto_balance.argtypes = [vp, i32]
+    L.vcb_balance_bounds.argtypes = [C.POINTER(C.c_uint64), i32, i32, i32, i32, ip]
     L.vcb_sharded_reset.argtypes = [vp]
     L.vcb_sharded_carve_masks.argtypes = [vp, i32, C.POINTER(View), pp, pp]
     L.vcb_sharded_carve_masks_device.argtypes = [vp, i32, C.POINTER(View), pp, pp]

@@ -451,21 +451,7 @@ int place_boundaries(vcb_sharded* s, int cnt, int J, int h) {
   }
   if (total == 0) return VCB_OK;
   std::vector<int> b(N + 1, 0);
-  b[N] = s->nz;
-  uint64_t run = 0;
-  int layer = 0;
-  for (int r = 1; r < N; r++) {
-    // first layer boundary at which the running cost reaches r / N of the total (or the one before
-    // it, whichever is closer), leaving at least one layer to every slab still to come
-    const uint64_t target = total / N * r;
-    while (layer < layers && run + cost[layer] <= target) run += cost[layer++];
-    int k = layer;
-    if (k < layers && target - run > run + cost[k] - target) k++;
-    const int lo = b[r - 1] / q + 1, hi = layers - (N - r);
-    k = k < lo ? lo : (k > hi ? hi : k);
-    b[r] = k * q;
-    while (layer < k) run += cost[layer++];
-  }
+  if (vcb_balance_bounds(cost.data(), layers, q, s->nz, N, b.data()) != VCB_OK) return VCB_OK;
   if (b == s->bounds) return VCB_OK;
   int rc = check_bounds(s, b);
   if (rc != VCB_OK) return rc;
@@ -974,6 +960,32 @@ int vcb_sharded_local(vcb_sharded* s, int32_t i, vcb_carver** carver, int32_t* r
   if (!s || i < 0 || i >= (int)s->local.size()) return sfail(s, VCB_ERR_INVALID, "no such local slab");
   if (carver) *carver = s->local[i].car;
   if (rank) *rank = s->local[i].rank;
+  return VCB_OK;
+}
+
+int vcb_balance_bounds(const uint64_t* layer_cost, int32_t n_layers, int32_t planes_per_layer,
+                       int32_t nz, int32_t world, int32_t* z_bounds) {
+  if (!layer_cost || !z_bounds || world < 1 || planes_per_layer < 1 || n_layers < world ||
+      (int64_t)n_layers * planes_per_layer < nz || (int64_t)(n_layers - 1) * planes_per_layer >= nz)
+    return sfail(nullptr, VCB_ERR_INVALID, "vcb_balance_bounds: bad argument");
+  uint64_t total = 0;
+  for (int i = 0; i < n_layers; i++) total += layer_cost[i];
+  z_bounds[0] = 0;
+  z_bounds[world] = nz;
+  uint64_t run = 0;
+  int layer = 0;
+  for (int r = 1; r < world; r++) {
+    // first layer boundary at which the running cost reaches r / world of the total (or the one
+    // before it, whichever is closer), leaving at least one layer to every slab still to come
+    const uint64_t target = total / world * r;
+    while (layer < n_layers && run + layer_cost[layer] <= target) run += layer_cost[layer++];
+    int k = layer;
+    if (k < n_layers && target - run > run + layer_cost[k] - target) k++;
+    const int lo = z_bounds[r - 1] / planes_per_layer + 1, hi = n_layers - (world - r);
+    k = k < lo ? lo : (k > hi ? hi : k);
+    z_bounds[r] = k * planes_per_layer;
+    while (layer < k) run += layer_cost[layer++];
+  }
   return VCB_OK;
 }
 
