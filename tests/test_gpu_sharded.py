@@ -248,7 +248,7 @@ def test_engine_on_two_real_devices_when_present(cuda_lib, port):
         eng.close()
 
 
-def test_engine_auto_balance_places_boundaries_and_keeps_the_result(cuda_lib, port):
+def test_engine_auto_balance_places_boundaries_and_keeps_the_result(cuda_lib, port, tmp_path):
     """vcb_sharded_set_auto_balance: the boundaries move (whole fusion tiles of 8 planes, the ends of
     the grid get thicker slabs than the middle, which sees the object) before the first chunk is
     fused - and the result is still the oracle's, bit for bit."""
@@ -281,3 +281,14 @@ def test_engine_auto_balance_places_boundaries_and_keeps_the_result(cuda_lib, po
     # a later pass keeps the partition
     eng.reset()
     assert eng.carve_batch(cams[:5], masks[:5]) and eng.ranges == moved
+    # the same through the file path (the sample files are decoded first)
+    from tests.test_ingest_host import write_png
+    paths = []
+    for i, m in enumerate(masks):
+        paths.append(tmp_path / ("m%03d.png" % i))
+        write_png(paths[-1], m, filters=(0,), level=1)
+    eng2 = sharded.LocalSlabs(o, 4)
+    eng2.set_auto_balance(True)
+    assert eng2.carve_files(cams, paths, (512, 512)) and eng2.ranges == moved
+    gs, gn = eng2.download_grid()
+    assert np.array_equal(gn, wn) and bits_equal(gs, ws)

@@ -652,30 +652,52 @@ int queue_view(vcb_sharded* s, const vcb_view& v, const uint8_t* mask, bool devi
   return VCB_OK;
 }
 
+// ---- auto-balance from a sample of a long call's views ---------------------------------------------
+bool wants_probe(const vcb_sharded* s, int n_views) {
+  return s->balance_pending && s->world > 1 && n_views > s->chunk_cap && s->queued == 0;
+}
+// k-th of the chunk_cap sample views of a call with n_views views (evenly spread)
+int probe_index(const vcb_sharded* s, int k, int n_views) {
+  return (int)((int64_t)k * n_views / s->chunk_cap);
+}
+// Transforms and gathers exactly one chunk of sample views (sample k is owned by rank k mod world,
+// only owners read their mask), places the slab boundaries from its tile classes and forgets it.
+int run_probe(vcb_sharded* s, const vcb_view* sample_views, const uint8_t* const* sample_masks,
+              bool device_io) {
+  s->probing = true;
+  int rc = VCB_OK;
+  for (int k = 0; k < s->chunk_cap && rc == VCB_OK; k++) {
+    rc = queue_view(s, sample_views[k], sample_masks[k], device_io);  // the last one flushes
+  }
+  s->probing = false;
+  s->queued = 0;
+  if (rc != VCB_OK) return rc;
+  if (!device_io) {  // the sample's host masks are borrowed until the copies are done
+    for (auto& L : s->local) {
+      SCU(s, cudaSetDevice(L.device));
+      SCU(s, cudaStreamSynchronize(L.copy));
+    }
+  }
+  return VCB_OK;
+}
+
 int carve_impl(vcb_sharded* s, int32_t n_views, const vcb_view* views, const uint8_t* const* masks,
                float* const* sdf_out, bool device_io) {
   if (!s) return sfail(nullptr, VCB_ERR_INVALID, "null handle");
   if (n_views < 0 || (n_views > 0 && (!views || !masks))) return sfail(s, VCB_ERR_INVALID, "null argument");
   bool want_sdf = false;
   for (int i = 0; sdf_out && i < n_views; i++) want_sdf = want_sdf || sdf_out[i] != nullptr;
-  if (s->balance_pending && s->world > 1 && n_views > s->chunk_cap && s->queued == 0 && !want_sdf) {
+  if (wants_probe(s, n_views) && !want_sdf) {
     // Auto-balance with many views in one call: the first chunk alone may see the grid from one
     // side only (a turntable's first 64 views), so the estimate uses views spread over the call.
-    s->probing = true;
-    int rc = VCB_OK;
-    for (int k = 0; k < s->chunk_cap && rc == VCB_OK; k++) {
-      const int i = (int)((int64_t)k * n_views / s->chunk_cap);
-      rc = queue_view(s, views[i], masks[i], device_io);  // the last one flushes (probe branch)
+    std::vector<vcb_view> sv(s->chunk_cap);
+    std::vector<const uint8_t*> sm(s->chunk_cap);
+    for (int k = 0; k < s->chunk_cap; k++) {
+      sv[k] = views[probe_index(s, k, n_views)];
+      sm[k] = masks[probe_index(s, k, n_views)];
     }
-    s->probing = false;
-    s->queued = 0;
+    int rc = run_probe(s, sv.data(), sm.data(), device_io);
     if (rc != VCB_OK) return rc;
-    if (!device_io) {
-      for (auto& L : s->local) {
-        SCU(s, cudaSetDevice(L.device));
-        SCU(s, cudaStreamSynchronize(L.copy));
-      }
-    }
   }
   for (int i = 0; i < n_views; i++) {
     if (want_sdf && sdf_out[i]) {
@@ -1076,6 +1098,24 @@ int vcb_sharded_carve_mask_files(vcb_sharded* s, int32_t n_views, const vcb_view
   const int batch = s->chunk_cap;
   SCU(s, s->ingest_pin.reserve(stride * (size_t)std::min(batch, std::max(n_views, 1))));
   uint8_t* pin = static_cast<uint8_t*>(s->ingest_pin.ptr);
+  if (wants_probe(s, n_views)) {
+    // auto-balance: decode the sample files (each process those it owns in the sample chunk) first
+    std::vector<vcb_view> sv(batch);
+    std::vector<const char*> sp(batch);
+    std::vector<char> mine(batch);
+    std::vector<const uint8_t*> sm(batch);
+    for (int k = 0; k < batch; k++) {
+      sv[k] = views[probe_index(s, k, n_views)];
+      sp[k] = paths[probe_index(s, k, n_views)];
+      mine[k] = local_of(s, k % s->world) != nullptr;
+      sm[k] = pin + (size_t)k * stride;
+    }
+    std::string err;
+    int rc = decode_mask_batch(sp.data(), sv.data(), batch, reinterpret_cast<const bool*>(mine.data()),
+                               pin, stride, n_threads, &err);
+    if (rc != VCB_OK) return sfail(s, rc, "%s", err.c_str());
+    if ((rc = run_probe(s, sv.data(), sm.data(), false)) != VCB_OK) return rc;
+  }
   for (int first = 0; first < n_views; first += batch) {
     const int nb = std::min(batch, n_views - first);
     int rc = flush_chunk(s);
