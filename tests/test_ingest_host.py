@@ -128,3 +128,31 @@ def test_bundled_bunny_masks_when_present(bunny):
         pytest.skip("oracle/_ref/data not present")
     for i in range(6):
         assert np.array_equal(load_mask_file(os.path.join(root, "mask_%05d.png" % i)), bunny.masks[i])
+
+
+def test_damaged_files_never_crash(tmp_path):
+    """The decoder reads files it did not write: random byte damage anywhere in a PNG (header, zlib
+    stream, Huffman tables, chunk lengths) must end in a clean error or in some image, never in a
+    crash or an out-of-bounds write (the output buffer is sized from the damaged header itself)."""
+    rng = np.random.default_rng(99)
+    yy, xx = np.mgrid[0:120, 0:160]
+    img = (((yy - 60) ** 2 + (xx - 70) ** 2 < 1500) * 255).astype(np.uint8)
+    img[::7, ::5] = rng.integers(0, 256, img[::7, ::5].shape, dtype=np.uint8)
+    write_png(tmp_path / "good.png", img, (0, 1, 2, 3, 4), 6, idat_split=2)
+    good = open(tmp_path / "good.png", "rb").read()
+    outcomes = {"ok": 0, "error": 0}
+    for t in range(400):
+        data = bytearray(good)
+        for _ in range(int(rng.integers(1, 4))):
+            data[int(rng.integers(8, len(data)))] = int(rng.integers(0, 256))
+        if t % 10 == 0:
+            data = data[:int(rng.integers(20, len(data)))]
+        open(tmp_path / "bad.png", "wb").write(bytes(data))
+        try:
+            out = load_mask_file(tmp_path / "bad.png")
+            assert out.ndim == 2
+            outcomes["ok"] += 1
+        except capi.VcbError as e:
+            assert e.code in (-1, -4)
+            outcomes["error"] += 1
+    assert outcomes["error"] > 50  # most damage is detected (sizes, codes, stream length)
