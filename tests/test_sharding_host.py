@@ -64,7 +64,9 @@ def _worker(rank, world, port, q):
     # the NCCL unique id the one-process-per-GPU engine is built from: made on rank 0 by the library,
     # carried to the other ranks by torch.distributed (the only job torch has on that path)
     uid = sharded.broadcast_unique_id(rank, world)
-    q.put((rank, off.tolist(), total.tolist(), uid))
+    # measured slab costs -> the same new partition on every rank
+    new = sharded.agreed_ranges(sharded.slab_ranges(1024, world), [60.0, 40.0][rank], world)
+    q.put((rank, off.tolist(), total.tolist(), uid, new))
     dist.destroy_process_group()
 
 
@@ -82,8 +84,9 @@ def test_count_exchange_world2_gloo():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, off, total, uid in res:
+    for rank, off, total, uid, new in res:
         assert off == [[0, 0], [100, 7]] and total == [300, 15]
+    assert res[0][4] == res[1][4] and res[0][4][0][1] % 8 == 0 and res[0][4][0][1] < 512
     assert len(res[0][3]) == 128 and res[0][3] == res[1][3] and any(res[0][3])
 
 

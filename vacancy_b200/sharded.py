@@ -88,6 +88,17 @@ def gather_offsets(nv, nf, world, group=None, device="cpu"):
     return exclusive_offsets(torch.stack(allc).cpu().numpy())
 
 
+def agreed_ranges(ranges, my_cost, world, group=None, device="cpu"):
+    """Every rank contributes the measured cost of its slab; all ranks get the same new partition
+    (whole fusion tiles) from the gathered costs."""
+    import torch
+    import torch.distributed as dist
+    mine = torch.tensor([float(my_cost)], dtype=torch.float64, device=device)
+    allc = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allc, mine, group=group)
+    return rebalanced_ranges(ranges, [float(t.item()) for t in allc], quantum=FUSION_TILE_PLANES)
+
+
 def assemble_ply(totals, parts):
     """totals = global (vertices, faces); parts = per-slab (vertex_text, face_text) in slab order."""
     from . import capi as _capi
@@ -414,11 +425,7 @@ class ShardedCarver(_Engine):
             return self.ranges
         torch = self.torch
         on = torch.device("cuda", self.device_index) if torch.distributed.get_backend(self.group) == "nccl" else "cpu"
-        mine = torch.tensor([float(my_cost)], dtype=torch.float64, device=on)
-        allc = [torch.empty_like(mine) for _ in range(self.world)]
-        torch.distributed.all_gather(allc, mine, group=self.group)
-        cost = [float(t.item()) for t in allc]
-        new = rebalanced_ranges(self.ranges, cost, quantum=FUSION_TILE_PLANES)
+        new = agreed_ranges(self.ranges, my_cost, self.world, self.group, on)
         if new != self.ranges:
             self.slabs = []
             self._check(self._lib.vcb_sharded_repartition(self._h, _bounds_array(new)))
